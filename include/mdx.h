@@ -1,0 +1,204 @@
+/*
+ * mdx.h — C ABI of libmdx_b200.so, the sm_100a kernel library behind the minddiffusion denoising hot path
+ * (UNetModel forward inside the PLMS / DPM-Solver++ / DDIM sampler loops).
+ *
+ * The reference (mindspore-lab/minddiffusion) has NO native/FFI layer: every op on the path is a MindSpore
+ * primitive called from Python.  The entry points below are therefore the operator-level
+ * boundary a maintainer would bind with ctypes in place of those primitives; each one cites the reference call
+ * site it replaces (paths relative to vision/stablediffusionv2/ unless noted).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes.  Every pointer is a DEVICE pointer unless its name ends in _host.
+ *  - The caller owns every buffer (inputs, outputs, scratch); the library allocates nothing.
+ *  - `stream` is a cudaStream_t passed as void*.  All work is enqueued on it; nothing synchronises.
+ *  - Return value: 0 = ok, negative = error (-22 invalid argument, -5 CUDA failure, -95 unsupported).
+ *    mdx_last_error() returns a thread-local message for the last failure.
+ *  - Activations are NHWC ("pixel-major"): a tensor [n, H, W, C] is a matrix of n*H*W pixel rows whose row
+ *    stride (in elements) is passed explicitly (ld*), so channel slices of wider buffers are valid operands.
+ *  - dtype codes: MDX_F32 = 0 (fp32 check mode), MDX_BF16 = 1.
+ */
+#ifndef MDX_H_
+#define MDX_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDX_F32 0
+#define MDX_BF16 1
+
+const char* mdx_last_error(void);
+int mdx_version(void);
+/* Number of kernels this library has launched in the calling process (all threads). bench.py reports it. */
+int64_t mdx_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Tensor-core implicit GEMM (tcgen05.mma, TMEM accumulators, TMA-fed, persistent).
+ *   out[p, n] = epilogue( sum_seg sum_tap sum_c A_seg[pixel(p)+tap][c] * B[n][koff(seg,tap,c)] )
+ * Replaces nn.Conv2d 3x3/1x1 (ldm/modules/diffusionmodules/util.py:38-52, openaimodel.py:151-174,205),
+ * nn.Dense (util.py:31-35; ldm/modules/attention.py:44,108-114,63-67) and the ResBlock residual add
+ * (openaimodel.py:205) / GEGLU product (attention.py:47-51) / emb add (openaimodel.py:199-200) as epilogues.
+ *
+ *  A: 1..3 K-segments. Segment s is a bf16 NHWC view [n_img, H, W, seg_c[s]] with pixel stride lda[s];
+ *     seg_taps[s] is 9 (3x3, pad 1, stride 1) or 1 (1x1 / dense). seg_c[s] % 64 == 0.
+ *     A dense matrix [M, K] is passed as n_img = 1, H = 1, W = M.
+ *  B: bf16 [N, Ktot] row-major (K contiguous), Ktot = sum_s taps_s * seg_c[s], K order (segment, tap=(r,s), c).
+ *  epilogue, in this order: + bias[n] (fp32, optional) ; + rowbias[img(p) * ld_rowbias + n] (fp32, optional)
+ *     ; geglu (optional): N is 2*I laid out per BLOCK_N tile as [value half | gate half] (see pack_geglu in
+ *     minddiffusion_b200/weights.py), out[p, j] = value * gelu_tanh(gate), out has I columns
+ *     ; + residual[p * ldr + n] (bf16, optional) ; store bf16 (out_dtype MDX_BF16) or fp32 (MDX_F32).
+ *  block_n: 0 = choose automatically; otherwise one of 64, 128, 160, 256 (geglu packing must match).
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct mdx_gemm_args {
+  int32_t nseg;
+  const void* a[3];
+  int64_t lda[3];
+  int32_t seg_c[3];
+  int32_t seg_taps[3];
+  int32_t n_img, H, W;
+  const void* b;
+  int32_t N;
+  void* out;
+  int64_t ldc;
+  int32_t out_dtype;
+  const float* bias;
+  const float* rowbias;
+  int64_t ld_rowbias;
+  const void* residual;
+  int64_t ldr;
+  int32_t geglu;
+  int32_t block_n;
+} mdx_gemm_args;
+int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
+/* BLOCK_N the library would pick for a GEMM with N output columns (needed to pack GEGLU weights). */
+int mdx_gemm_tc_pick_block_n(int32_t N, int32_t geglu);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * CUDA-core implicit-GEMM convolution / dense layer (any Cin/Cout, stride, padding, optional nearest-2x
+ * upsample of the input).  fp32 check mode for every conv/dense of the path, and in bf16 mode the layers
+ * tensor cores do not fit: conv_in (Cin=4, openaimodel.py:350-353), conv_out (Cout=4, openaimodel.py:521-526),
+ * the time-embedding MLP (openaimodel.py:340-345) and ResBlock emb_layers (openaimodel.py:153-160).
+ *  x: [n, H, W, Cin] (pixel stride ldx), dtype in_dtype; w: [Cout, kh*kw*Cin] same dtype as x, K order (r,s,c).
+ *  upsample != 0: x is read through ops.ResizeNearestNeighbor x2 (openaimodel.py:53-60): logical input is
+ *     [n, 2H, 2W, Cin] with src = dst >> 1.
+ *  out: [n, OH, OW, Cout] (pixel stride ldo), dtype out_dtype; bias/rowbias fp32 optional; residual has the
+ *     out dtype.  pre_silu != 0 applies SiLU to x on load (emb_layers: SiLU -> Dense).
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct mdx_conv_args {
+  const void* x;
+  int64_t ldx;
+  int32_t in_dtype;
+  int32_t n, H, W, Cin;
+  const void* w;
+  int32_t Cout, kh, kw, stride, pad, upsample, pre_silu;
+  void* out;
+  int64_t ldo;
+  int32_t out_dtype;
+  const float* bias;
+  const float* rowbias;
+  int64_t ld_rowbias;
+  const void* residual;
+  int64_t ldr;
+} mdx_conv_args;
+int mdx_conv_direct(const mdx_conv_args* args, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * GroupNorm (+ optional SiLU) over NHWC, optionally over the channel-concatenation of two tensors
+ * (the skip concat ops.Concat(axis=1) of openaimodel.py:566-571 is never materialised separately).
+ * Replaces GroupNorm32(32, C) fp32 + nn.SiLU (util.py:87-108; openaimodel.py:134-137,162-163,521-523) and
+ * Normalize (attention.py:83-84).  Statistics are biased (1/N) variance, accumulated in fp64.
+ *  x1: [n, HW, C1] (ld1), x2: [n, HW, C2] (ld2) or NULL with C2 = 0.  gamma/beta: fp32 [C1+C2].
+ *  out: [n, HW, C1+C2] with pixel stride ldo.  dtype applies to x1, x2 and out.
+ *  stats_scratch: caller-provided, >= n*groups*2 doubles; overwritten.
+ * --------------------------------------------------------------------------------------------------------- */
+int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2, int32_t n,
+                  int32_t HW, int32_t groups, float eps, const float* gamma, const float* beta, int32_t silu,
+                  void* out, int64_t ldo, int32_t dtype, double* stats_scratch, void* stream);
+
+/* LayerNorm over the last dim of [rows, C] (ldx/ldo row strides). Replaces nn.LayerNorm([dim], epsilon=1e-5)
+ * (attention.py:176-178).  Biased variance, fp32 statistics, one warp per row. */
+int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,
+                  const float* beta, void* out, int64_t ldo, int32_t dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Multi-head attention  o = softmax(q k^T * scale) v  without materialising q k^T
+ * (CrossAttention.construct, attention.py:117-166; heads are interleaved in the channel dim, so the
+ * rearange_in/out transposes at attention.py:124-133,154-163 become strides).
+ *  q: [batch, Nq, heads*d] (row stride ldq), k/v: [batch, Nk, heads*d] (ldk/ldv), o: [batch, Nq, heads*d] (ldo).
+ *  Batch strides are Nq*ldq etc. (tensors are dense over batch).  dtype MDX_BF16: flash kernel on mma.sync
+ *  tensor cores with fp32 softmax; MDX_F32: CUDA-core check-mode kernel.  d <= 160, d % 8 == 0.
+ * --------------------------------------------------------------------------------------------------------- */
+int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, void* o,
+                  int64_t ldo, int32_t batch, int32_t heads, int32_t Nq, int32_t Nk, int32_t d, float scale,
+                  int32_t dtype, void* stream);
+
+/* GEGLU product for check mode: out[m, j] = x[m, j] * gelu_tanh(x[m, I + j]) (attention.py:47-51). */
+int mdx_geglu(const void* x, int64_t ldx, int32_t rows, int32_t I, void* out, int64_t ldo, int32_t dtype,
+              void* stream);
+
+/* Sinusoidal timestep embedding [cos | sin], fp32 (util.py:111-131). t: fp32 [n] (may be fractional). */
+int mdx_timestep_embedding(const float* t, int32_t n, int32_t dim, float max_period, float* out, void* stream);
+
+/* Layout / dtype movers.
+ *  mdx_nchw_to_nhwc: x fp32 NCHW [n, C, H, W] -> out [n*repeat, H, W, C] (dtype), batch index taken mod n:
+ *     the CFG ops.concat((x, x)) of plms.py:192 without a copy of its own.
+ *  mdx_nhwc_to_nchw: x [n, H, W, C] (dtype) -> fp32 NCHW.
+ *  mdx_upsample_nearest2x: ops.ResizeNearestNeighbor (openaimodel.py:53-60) on NHWC.
+ *  mdx_concat_channels: ops.Concat(axis=1) (openaimodel.py:567) on NHWC rows.
+ *  mdx_im2col3x3: gathers 3x3 patches (stride, pad 1) into [n*OH*OW, 9*C] rows, K order (r,s,c) — feeds the
+ *     stride-2 Downsample conv (openaimodel.py:80-88) to mdx_gemm_tc.
+ *  mdx_cast: elementwise fp32 <-> bf16 conversion of count elements. */
+int mdx_nchw_to_nhwc(const float* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t repeat, void* out,
+                     int32_t dtype, void* stream);
+/* same, output rows padded with zeros to Cpad >= C channels (conv_in, Cin = 4, is fed to mdx_gemm_tc as 64) */
+int mdx_nchw_to_nhwc_pad(const float* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t repeat, int32_t Cpad,
+                         void* out, int32_t dtype, void* stream);
+int mdx_nhwc_to_nchw(const void* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t dtype, float* out,
+                     void* stream);
+/* same, reading the first C channels of rows with pixel stride ldx >= C */
+int mdx_nhwc_to_nchw_ld(const void* x, int64_t ldx, int32_t n, int32_t C, int32_t H, int32_t W, int32_t dtype,
+                        float* out, void* stream);
+int mdx_upsample_nearest2x(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, void* out, int32_t dtype,
+                           void* stream);
+int mdx_concat_channels(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
+                        int64_t rows, void* out, int64_t ldo, int32_t dtype, void* stream);
+int mdx_im2col3x3(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, int32_t stride, void* out,
+                  int32_t dtype, void* stream);
+int mdx_cast(const void* x, int32_t in_dtype, void* out, int32_t out_dtype, int64_t count, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Sampler arithmetic: ONE elementwise kernel per step (classifier-free-guidance combine + latent update).
+ *
+ * mdx_sampler_plms_step — PLMSSampler.p_sample_plms (ldm/models/diffusion/plms.py:182-248) and, with
+ *   w = {1,0,0,0}, the DDIM update (get_x_prev_and_pred_x0, plms.py:210-228).
+ *    eps_model: UNet output, NHWC [cfg ? 2B : B, h, w, C] with pixel stride ld_eps (dtype model_dtype); rows [0,B) are the
+ *       unconditional half, [B,2B) the conditional half (concat order of plms.py:192-194).
+ *    e_t    = cfg ? e_u + scale*(e_c - e_u) : eps            (plms.py:195-197)
+ *    e'     = w[0]*e_t + w[1]*old1 + w[2]*old2 + w[3]*old3    (plms.py:231-244; old* fp32 NCHW or NULL)
+ *    pred_x0 = (x - sqrt(1-a_t) e') / sqrt(a_t)
+ *    x_prev  = sqrt(a_prev) pred_x0 + sqrt(1 - a_prev - sigma^2) e' + sigma*noise   (noise NULL => 0)
+ *    coef_host[4] = {a_t, a_prev, sigma_t, sqrt_one_minus_a_t}; x, x_prev, pred_x0, e_t_out fp32 NCHW [B,C,h,w];
+ *    pred_x0 / e_t_out may be NULL.  x_prev may alias x.
+ *
+ * mdx_sampler_dpmpp2m_step — DPM-Solver++ multistep (dpm_solver/dpm_solver.py:256-329 model_wrapper,
+ *   366-373 data_prediction_fn, 488-520 first update, 742-777 second update).
+ *    out    = cfg-combined model output as above; model_type 0: noise = out; 1 ("v", dpm_solver.py:281-284):
+ *             noise = alpha_s*out + sigma_s*x
+ *    x0_cur = (x - sigma_s*noise) / alpha_s
+ *    x_next = c[2]*x + c[3]*x0_cur + c[4]*(x0_cur - x0_prev)      (x0_prev NULL => c[4] ignored)
+ *    coef_host[5] = {alpha_s, sigma_s, c_x, c_0, c_1}.  x0_cur is written (history for the next step).
+ * --------------------------------------------------------------------------------------------------------- */
+int mdx_sampler_plms_step(const void* eps_model, int64_t ld_eps, int32_t model_dtype, int32_t cfg, float scale, const float* x,
+                          const float* old1, const float* old2, const float* old3, const float* w_host,
+                          const float* coef_host, const float* noise, float* x_prev, float* pred_x0,
+                          float* e_t_out, int32_t B, int32_t C, int32_t h, int32_t w, void* stream);
+int mdx_sampler_dpmpp2m_step(const void* eps_model, int64_t ld_eps, int32_t model_dtype, int32_t cfg, float scale,
+                             int32_t model_type, const float* x, const float* x0_prev, const float* coef_host,
+                             float* x_next, float* x0_cur, int32_t B, int32_t C, int32_t h, int32_t w,
+                             void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDX_H_ */

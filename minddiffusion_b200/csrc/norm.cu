@@ -1,0 +1,266 @@
+// GroupNorm(+SiLU) and LayerNorm over NHWC rows: HBM-bound, 16-byte vectorised, coalesced along channels.
+// See include/mdx.h (mdx_groupnorm, mdx_layernorm) for the reference call sites.
+//
+// GroupNorm = two passes over the activation (the minimum without a persistent cooperative kernel):
+//   gn_stats_kernel : each thread owns one 16-byte channel vector and walks pixel rows; per-channel fp32
+//                     partial sums -> per-group smem bins -> fp64 atomics into stats[n][group][{sum,sumsq}]
+//   gn_apply_kernel : y = x * a_c + b_c (a,b folded from mean/rstd/gamma/beta), optional SiLU, store.
+// Both take two sources so the UNet skip concat (openaimodel.py:566-571) is normalised without a copy.
+#include "common.cuh"
+#include "../../include/mdx.h"
+#include <atomic>
+
+extern std::atomic<long long> g_mdx_launches;
+
+namespace {
+
+template <typename T> struct Vec;
+template <> struct Vec<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const float* p, float (&v)[4]) {
+    float4 u = *reinterpret_cast<const float4*>(p);
+    v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
+  }
+  __device__ static void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Vec<bf16> {
+  static constexpr int N = 8;
+  __device__ static void load(const bf16* p, float (&v)[8]) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    float2 f;
+    f = unpack_bf16x2(u.x); v[0] = f.x; v[1] = f.y;
+    f = unpack_bf16x2(u.y); v[2] = f.x; v[3] = f.y;
+    f = unpack_bf16x2(u.z); v[4] = f.x; v[5] = f.y;
+    f = unpack_bf16x2(u.w); v[6] = f.x; v[7] = f.y;
+  }
+  __device__ static void store(bf16* p, const float (&v)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+    u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+  }
+};
+
+struct GnP {
+  const void* x1; long long ld1; int C1;
+  const void* x2; long long ld2; int C2;
+  int n, HW, groups, cpg;
+  int rows_per_block;
+  float eps;
+  const float* gamma; const float* beta;
+  int silu;
+  void* out; long long ldo;
+  double* stats;
+};
+
+// blockDim = (CVr, RP): x = channel-vector index, y = row lane
+template <typename T>
+__global__ void gn_stats_kernel(const GnP p) {
+  constexpr int V = Vec<T>::N;
+  __shared__ float bins[64][2];
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y) (&bins[0][0])[i] = 0.f;
+  __syncthreads();
+  const int C = p.C1 + p.C2;
+  const int c0 = threadIdx.x * V;
+  const int img = blockIdx.y;
+  if (c0 < C) {
+    const T* src;
+    long long ld;
+    int cc;
+    if (c0 < p.C1) { src = reinterpret_cast<const T*>(p.x1); ld = p.ld1; cc = c0; }
+    else { src = reinterpret_cast<const T*>(p.x2); ld = p.ld2; cc = c0 - p.C1; }
+    const int r0 = blockIdx.x * p.rows_per_block;
+    const int r1 = min(p.HW, r0 + p.rows_per_block);
+    float s[V], ss[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) { s[i] = 0.f; ss[i] = 0.f; }
+    const T* base = src + (long long)img * p.HW * ld + cc;
+    for (int r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
+      float v[V];
+      Vec<T>::load(base + (long long)r * ld, v);
+#pragma unroll
+      for (int i = 0; i < V; ++i) { s[i] += v[i]; ss[i] = fmaf(v[i], v[i], ss[i]); }
+    }
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int g = (c0 + i) / p.cpg;
+      atomicAdd(&bins[g][0], s[i]);
+      atomicAdd(&bins[g][1], ss[i]);
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y)
+    atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (double)(&bins[0][0])[i]);
+}
+
+template <typename T>
+__global__ void gn_apply_kernel(const GnP p) {
+  constexpr int V = Vec<T>::N;
+  const int C = p.C1 + p.C2;
+  const int c0 = threadIdx.x * V;
+  const int img = blockIdx.y;
+  if (c0 >= C) return;
+  const T* src;
+  long long ld;
+  int cc;
+  if (c0 < p.C1) { src = reinterpret_cast<const T*>(p.x1); ld = p.ld1; cc = c0; }
+  else { src = reinterpret_cast<const T*>(p.x2); ld = p.ld2; cc = c0 - p.C1; }
+  float a[V], b[V];
+  const double cnt = (double)p.HW * p.cpg;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = c0 + i;
+    const int g = c / p.cpg;
+    const double sum = p.stats[((long long)img * p.groups + g) * 2];
+    const double sq = p.stats[((long long)img * p.groups + g) * 2 + 1];
+    const double mean = sum / cnt;
+    double var = sq / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
+    a[i] = rstd * p.gamma[c];
+    b[i] = p.beta[c] - (float)mean * a[i];
+  }
+  const int r0 = blockIdx.x * p.rows_per_block;
+  const int r1 = min(p.HW, r0 + p.rows_per_block);
+  const T* base = src + (long long)img * p.HW * ld + cc;
+  T* obase = reinterpret_cast<T*>(p.out) + (long long)img * p.HW * p.ldo + c0;
+  for (int r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
+    float v[V];
+    Vec<T>::load(base + (long long)r * ld, v);
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      float y = fmaf(v[i], a[i], b[i]);
+      v[i] = p.silu ? silu_f(y) : y;
+    }
+    Vec<T>::store(obase + (long long)r * p.ldo, v);
+  }
+}
+
+// ---------------- LayerNorm: one warp per row, values held in registers ----------------
+template <typename T, int MAXV>
+__global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, long long ldx, int rows, int C,
+                                                        float eps, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, T* __restrict__ out,
+                                                        long long ldo) {
+  constexpr int V = Vec<T>::N;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const int nvec = C / V;
+  const T* xr = x + (long long)warp * ldx;
+  float v[MAXV][V];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int vi = lane + j * 32;
+    if (vi < nvec) {
+      Vec<T>::load(xr + vi * V, v[j]);
+#pragma unroll
+      for (int i = 0; i < V; ++i) s += v[j][i];
+    }
+  }
+  s = warp_sum(s);
+  const float mean = s / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int vi = lane + j * 32;
+    if (vi < nvec) {
+#pragma unroll
+      for (int i = 0; i < V; ++i) { float d = v[j][i] - mean; q = fmaf(d, d, q); }
+    }
+  }
+  q = warp_sum(q);
+  const float rstd = rsqrtf(q / (float)C + eps);
+  T* orow = out + (long long)warp * ldo;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int vi = lane + j * 32;
+    if (vi < nvec) {
+      float y[V];
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const int c = vi * V + i;
+        y[i] = (v[j][i] - mean) * rstd * gamma[c] + beta[c];
+      }
+      Vec<T>::store(orow + vi * V, y);
+    }
+  }
+}
+
+template <typename T>
+int launch_gn(GnP p, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const int C = p.C1 + p.C2;
+  const int CV = C / V;
+  const int CVr = ((CV + 31) / 32) * 32;
+  MDX_CHECK_ARG(CVr <= 1024, "mdx_groupnorm: too many channels (%d)", C);
+  int RP = 512 / CVr;
+  if (RP < 1) RP = 1;
+  if (RP > 16) RP = 16;
+  // enough blocks to fill the machine, but at least 4*RP rows each
+  int chunks = (p.HW + 4 * RP - 1) / (4 * RP);
+  int want = (4 * 148 + p.n - 1) / p.n;
+  if (chunks > want) chunks = want;
+  if (chunks < 1) chunks = 1;
+  p.rows_per_block = (p.HW + chunks - 1) / chunks;
+  chunks = (p.HW + p.rows_per_block - 1) / p.rows_per_block;
+  dim3 grid(chunks, p.n), block(CVr, RP);
+  MDX_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, sizeof(double) * 2 * p.groups * p.n, st));
+  gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
+  MDX_CHECK_LAUNCH();
+  gn_apply_kernel<T><<<grid, block, 0, st>>>(p);
+  MDX_CHECK_LAUNCH();
+  g_mdx_launches.fetch_add(2, std::memory_order_relaxed);
+  return MDX_OK;
+}
+
+}  // namespace
+
+extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
+                             int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma,
+                             const float* beta, int32_t silu, void* out, int64_t ldo, int32_t dtype,
+                             double* stats_scratch, void* stream) {
+  MDX_CHECK_ARG(x1 && out && gamma && beta && stats_scratch, "mdx_groupnorm: NULL operand");
+  MDX_CHECK_ARG(n > 0 && HW > 0 && C1 > 0 && C2 >= 0, "mdx_groupnorm: empty problem");
+  MDX_CHECK_ARG(C2 == 0 || x2 != nullptr, "mdx_groupnorm: x2 is NULL but C2 > 0");
+  const int C = C1 + C2;
+  MDX_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "mdx_groupnorm: C=%d not divisible by groups=%d", C,
+                groups);
+  const int V = dtype == MDX_BF16 ? 8 : 4;
+  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_groupnorm: bad dtype");
+  MDX_CHECK_ARG(C1 % V == 0 && C2 % V == 0 && ld1 % V == 0 && ld2 % V == 0 && ldo % V == 0,
+                "mdx_groupnorm: channels and row strides must be multiples of %d", V);
+  MDX_CHECK_ARG(((uintptr_t)x1 & 15) == 0 && ((uintptr_t)x2 & 15) == 0 && ((uintptr_t)out & 15) == 0,
+                "mdx_groupnorm: operands must be 16-byte aligned");
+  GnP p;
+  p.x1 = x1; p.ld1 = ld1; p.C1 = C1; p.x2 = x2; p.ld2 = ld2; p.C2 = C2;
+  p.n = n; p.HW = HW; p.groups = groups; p.cpg = C / groups; p.rows_per_block = 0;
+  p.eps = eps; p.gamma = gamma; p.beta = beta; p.silu = silu; p.out = out; p.ldo = ldo; p.stats = stats_scratch;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  return dtype == MDX_BF16 ? launch_gn<bf16>(p, st) : launch_gn<float>(p, st);
+}
+
+extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,
+                             const float* beta, void* out, int64_t ldo, int32_t dtype, void* stream) {
+  MDX_CHECK_ARG(x && out && gamma && beta, "mdx_layernorm: NULL operand");
+  MDX_CHECK_ARG(rows > 0 && C > 0, "mdx_layernorm: empty problem");
+  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_layernorm: bad dtype");
+  const int V = dtype == MDX_BF16 ? 8 : 4;
+  MDX_CHECK_ARG(C % V == 0 && ldx % V == 0 && ldo % V == 0, "mdx_layernorm: C and strides must be multiples of %d", V);
+  MDX_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0, "mdx_layernorm: 16-byte alignment");
+  MDX_CHECK_ARG(C / V <= 12 * 32, "mdx_layernorm: C=%d too large", C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int wpb = 8;
+  dim3 grid((rows + wpb - 1) / wpb), block(wpb * 32);
+  if (dtype == MDX_BF16)
+    layernorm_kernel<bf16, 12><<<grid, block, 0, st>>>((const bf16*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
+  else
+    layernorm_kernel<float, 12><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (float*)out, ldo);
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}
