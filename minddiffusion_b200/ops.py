@@ -1,0 +1,345 @@
+"""Operator layer: torch tensors in, sm_100a kernels (through the C ABI) out.
+
+PyTorch is used for tensor ownership and the current CUDA stream only; every function here enqueues one or
+more kernels of libmdx_b200.so.  Activations are NHWC: ``[n, H, W, C]`` or, flattened, ``[rows, C]``; the last
+dim must be contiguous and the row stride uniform, so channel slices of wider buffers are valid operands.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ConvArgs, GemmArgs, check
+
+F32, BF16 = 0, 1
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _dt(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError("unsupported dtype %s (need float32 or bfloat16)" % t.dtype)
+
+
+def _rows_ld(t):
+    """(rows, C, ld) of an NHWC / [rows, C] view; raises unless rows are uniformly strided."""
+    if not t.is_cuda:
+        raise ValueError("expected a CUDA tensor (there is no CPU path)")
+    if t.dim() < 2 or t.stride(-1) != 1:
+        raise ValueError("last dim must be contiguous")
+    ld = t.stride(-2)
+    rows = t.size(-2)
+    for d in range(t.dim() - 3, -1, -1):
+        if t.size(d) != 1 and t.stride(d) != t.stride(d + 1) * t.size(d + 1):
+            raise ValueError("rows of the view are not uniformly strided: %s %s" % (tuple(t.shape), t.stride()))
+        rows *= t.size(d)
+    return rows, t.size(-1), ld
+
+
+def _f32(t, name):
+    if t is None:
+        return None
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise TypeError("%s must be contiguous float32" % name)
+    return t
+
+
+def pick_block_n(N, geglu=False):
+    return int(_lib.load().mdx_gemm_tc_pick_block_n(N, 1 if geglu else 0))
+
+
+def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
+            block_n=0):
+    """Tensor-core implicit GEMM (mdx_gemm_tc).
+
+    segs: list of (a, taps); a is bf16 ``[n, H, W, C]`` (conv view) or ``[M, C]`` (dense), taps 9 or 1.
+    weight: bf16 ``[N, Ktot]``.  rowbias: fp32 ``[n_img, N]`` view (row stride may exceed N).
+    """
+    lib = _lib.load()
+    a0 = segs[0][0]
+    if a0.dim() == 4:
+        n_img, H, W = a0.shape[0], a0.shape[1], a0.shape[2]
+    else:
+        n_img, H, W = 1, 1, a0.shape[0]
+    args = GemmArgs()
+    args.nseg = len(segs)
+    for i, (a, taps) in enumerate(segs):
+        if a.dtype != torch.bfloat16:
+            raise TypeError("gemm_tc operands must be bfloat16")
+        rows, C, ld = _rows_ld(a)
+        if rows != n_img * H * W:
+            raise ValueError("segment %d has %d rows, expected %d" % (i, rows, n_img * H * W))
+        args.a[i] = a.data_ptr()
+        args.lda[i] = ld
+        args.seg_c[i] = C
+        args.seg_taps[i] = taps
+    if weight.dtype != torch.bfloat16 or not weight.is_contiguous():
+        raise TypeError("weight must be contiguous bfloat16 [N, K]")
+    N = weight.shape[0]
+    ktot = sum(taps * a.shape[-1] for a, taps in segs)
+    if weight.shape[1] != ktot:
+        raise ValueError("weight K=%d does not match segments K=%d" % (weight.shape[1], ktot))
+    n_out = N // 2 if geglu else N
+    M = n_img * H * W
+    if out is None:
+        out = torch.empty((M, n_out), dtype=out_dtype, device=a0.device)
+    orow, oc, ldc = _rows_ld(out)
+    if orow != M or oc != n_out:
+        raise ValueError("out has shape %s, expected [%d, %d]" % (tuple(out.shape), M, n_out))
+    args.n_img, args.H, args.W = n_img, H, W
+    args.b = weight.data_ptr()
+    args.N = N
+    args.out = out.data_ptr()
+    args.ldc = ldc
+    args.out_dtype = _dt(out)
+    args.bias = _f32(bias, "bias").data_ptr() if bias is not None else None
+    if rowbias is not None:
+        if rowbias.dtype != torch.float32 or rowbias.stride(-1) != 1:
+            raise TypeError("rowbias must be float32 with contiguous last dim")
+        args.rowbias = rowbias.data_ptr()
+        args.ld_rowbias = rowbias.stride(0)
+    if residual is not None:
+        if residual.dtype != torch.bfloat16:
+            raise TypeError("residual must be bfloat16")
+        rr, rc, ldr = _rows_ld(residual)
+        if rr != M or rc != n_out:
+            raise ValueError("residual shape mismatch")
+        args.residual = residual.data_ptr()
+        args.ldr = ldr
+    args.geglu = 1 if geglu else 0
+    args.block_n = block_n
+    check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
+    return out
+
+
+def conv_direct(x, w, kh=1, kw=1, stride=1, pad=0, upsample=False, pre_silu=False, bias=None, rowbias=None,
+                residual=None, out=None, out_dtype=None):
+    """CUDA-core implicit-GEMM conv/dense (mdx_conv_direct). x: [n,H,W,Cin] or [M,Cin]; w: [Cout, kh*kw*Cin]."""
+    lib = _lib.load()
+    if x.dim() == 4:
+        n, H, W = x.shape[0], x.shape[1], x.shape[2]
+    else:
+        n, H, W = 1, 1, x.shape[0]
+    rows, Cin, ldx = _rows_ld(x)
+    Cout = w.shape[0]
+    if w.dtype != x.dtype or not w.is_contiguous() or w.shape[1] != kh * kw * Cin:
+        raise ValueError("weight must be contiguous [Cout, kh*kw*Cin] with the dtype of x")
+    Hl, Wl = (2 * H, 2 * W) if upsample else (H, W)
+    OH = (Hl + 2 * pad - kh) // stride + 1
+    OW = (Wl + 2 * pad - kw) // stride + 1
+    if out is None:
+        odt = out_dtype or x.dtype
+        out = torch.empty((n, OH, OW, Cout) if x.dim() == 4 else (OW, Cout), dtype=odt, device=x.device)
+    orow, oc, ldo = _rows_ld(out)
+    if orow != n * OH * OW or oc != Cout:
+        raise ValueError("out shape mismatch")
+    a = ConvArgs()
+    a.x, a.ldx, a.in_dtype = x.data_ptr(), ldx, _dt(x)
+    a.n, a.H, a.W, a.Cin = n, H, W, Cin
+    a.w = w.data_ptr()
+    a.Cout, a.kh, a.kw, a.stride, a.pad = Cout, kh, kw, stride, pad
+    a.upsample, a.pre_silu = int(upsample), int(pre_silu)
+    a.out, a.ldo, a.out_dtype = out.data_ptr(), ldo, _dt(out)
+    a.bias = _f32(bias, "bias").data_ptr() if bias is not None else None
+    if rowbias is not None:
+        if rowbias.dtype != torch.float32 or rowbias.stride(-1) != 1:
+            raise TypeError("rowbias must be float32 with contiguous last dim")
+        a.rowbias, a.ld_rowbias = rowbias.data_ptr(), rowbias.stride(0)
+    if residual is not None:
+        if residual.dtype != out.dtype:
+            raise TypeError("residual must have the out dtype")
+        rr, rc, ldr = _rows_ld(residual)
+        a.residual, a.ldr = residual.data_ptr(), ldr
+    check(lib.mdx_conv_direct(ctypes.byref(a), _stream()), "mdx_conv_direct")
+    return out
+
+
+def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=None, scratch=None):
+    """GroupNorm(+SiLU) over NHWC ``[n, H, W, C]`` (optionally over concat(x1, x2) along C)."""
+    lib = _lib.load()
+    n = x1.shape[0]
+    rows, C1, ld1 = _rows_ld(x1)
+    HW = rows // n
+    C2, ld2 = 0, 0
+    if x2 is not None:
+        r2, C2, ld2 = _rows_ld(x2)
+        if r2 != rows or x2.dtype != x1.dtype:
+            raise ValueError("x2 must match x1 in rows and dtype")
+    if out is None:
+        out = torch.empty(tuple(x1.shape[:-1]) + (C1 + C2,), dtype=x1.dtype, device=x1.device)
+    _, oc, ldo = _rows_ld(out)
+    if oc != C1 + C2:
+        raise ValueError("out channel mismatch")
+    if scratch is None:
+        scratch = torch.empty(n * groups * 2, dtype=torch.float64, device=x1.device)
+    elif scratch.dtype != torch.float64 or scratch.numel() < n * groups * 2:
+        raise ValueError("scratch must hold n*groups*2 float64")
+    check(lib.mdx_groupnorm(_p(x1), ld1, C1, _p(x2), ld2, C2, n, HW, groups, float(eps), _p(_f32(gamma, "gamma")),
+                            _p(_f32(beta, "beta")), int(silu), _p(out), ldo, _dt(x1), _p(scratch), _stream()),
+          "mdx_groupnorm")
+    return out
+
+
+def layernorm(x, gamma, beta, eps=1e-5, out=None):
+    lib = _lib.load()
+    rows, C, ldx = _rows_ld(x)
+    if out is None:
+        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    _, _, ldo = _rows_ld(out)
+    check(lib.mdx_layernorm(_p(x), ldx, rows, C, float(eps), _p(_f32(gamma, "gamma")), _p(_f32(beta, "beta")),
+                            _p(out), ldo, _dt(x), _stream()), "mdx_layernorm")
+    return out
+
+
+def attention(q, k, v, heads, scale, out=None):
+    """q: [B, Nq, heads*d] view, k/v: [B, Nk, heads*d] views (dense over batch). Returns [B, Nq, heads*d]."""
+    lib = _lib.load()
+    B, Nq, HDm = q.shape
+    Nk = k.shape[1]
+    d = HDm // heads
+    for t, nm, nn in ((q, "q", Nq), (k, "k", Nk), (v, "v", Nk)):
+        if t.stride(-1) != 1 or (B > 1 and t.stride(0) != t.stride(1) * nn):
+            raise ValueError("%s must be dense over batch with contiguous channels" % nm)
+    if out is None:
+        out = torch.empty((B, Nq, HDm), dtype=q.dtype, device=q.device)
+    check(lib.mdx_attention(_p(q), q.stride(1), _p(k), k.stride(1), _p(v), v.stride(1), _p(out), out.stride(1), B,
+                            heads, Nq, Nk, d, float(scale), _dt(q), _stream()), "mdx_attention")
+    return out
+
+
+def geglu(x, out=None):
+    lib = _lib.load()
+    rows, C2, ldx = _rows_ld(x)
+    I = C2 // 2
+    if out is None:
+        out = torch.empty(tuple(x.shape[:-1]) + (I,), dtype=x.dtype, device=x.device)
+    _, _, ldo = _rows_ld(out)
+    check(lib.mdx_geglu(_p(x), ldx, rows, I, _p(out), ldo, _dt(x), _stream()), "mdx_geglu")
+    return out
+
+
+def timestep_embedding(t, dim, max_period=10000.0):
+    lib = _lib.load()
+    t = _f32(t, "t")
+    out = torch.empty((t.shape[0], dim), dtype=torch.float32, device=t.device)
+    check(lib.mdx_timestep_embedding(_p(t), t.shape[0], dim, float(max_period), _p(out), _stream()),
+          "mdx_timestep_embedding")
+    return out
+
+
+def nchw_to_nhwc(x, dtype, repeat=1, cpad=None):
+    lib = _lib.load()
+    x = _f32(x, "x")
+    n, C, H, W = x.shape
+    cp = cpad or C
+    out = torch.empty((n * repeat, H, W, cp), dtype=dtype, device=x.device)
+    check(lib.mdx_nchw_to_nhwc_pad(_p(x), n, C, H, W, repeat, cp, _p(out), _DT[dtype], _stream()), "mdx_nchw_to_nhwc")
+    return out
+
+
+def nhwc_to_nchw(x, C=None):
+    """x: [n, H, W, ld] -> fp32 [n, C, H, W] taking the first C channels."""
+    lib = _lib.load()
+    n, H, W, ld = x.shape
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    C = C or ld
+    out = torch.empty((n, C, H, W), dtype=torch.float32, device=x.device)
+    check(lib.mdx_nhwc_to_nchw_ld(_p(x), ld, n, C, H, W, _dt(x), _p(out), _stream()), "mdx_nhwc_to_nchw")
+    return out
+
+
+def upsample_nearest2x(x):
+    lib = _lib.load()
+    n, H, W, C = x.shape
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    out = torch.empty((n, 2 * H, 2 * W, C), dtype=x.dtype, device=x.device)
+    check(lib.mdx_upsample_nearest2x(_p(x), n, H, W, C, _p(out), _dt(x), _stream()), "mdx_upsample_nearest2x")
+    return out
+
+
+def concat_channels(x1, x2):
+    lib = _lib.load()
+    r1, C1, ld1 = _rows_ld(x1)
+    r2, C2, ld2 = _rows_ld(x2)
+    if r1 != r2 or x1.dtype != x2.dtype:
+        raise ValueError("concat operands mismatch")
+    out = torch.empty(tuple(x1.shape[:-1]) + (C1 + C2,), dtype=x1.dtype, device=x1.device)
+    check(lib.mdx_concat_channels(_p(x1), ld1, C1, _p(x2), ld2, C2, r1, _p(out), C1 + C2, _dt(x1), _stream()),
+          "mdx_concat_channels")
+    return out
+
+
+def im2col3x3(x, stride):
+    lib = _lib.load()
+    n, H, W, C = x.shape
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    OH, OW = (H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1
+    out = torch.empty((n, OH, OW, 9 * C), dtype=x.dtype, device=x.device)
+    check(lib.mdx_im2col3x3(_p(x), n, H, W, C, stride, _p(out), _dt(x), _stream()), "mdx_im2col3x3")
+    return out
+
+
+def cast(x, dtype):
+    lib = _lib.load()
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    out = torch.empty(x.shape, dtype=dtype, device=x.device)
+    check(lib.mdx_cast(_p(x), _dt(x), _p(out), _DT[dtype], x.numel(), _stream()), "mdx_cast")
+    return out
+
+
+def _host_floats(vals):
+    arr = (ctypes.c_float * len(vals))(*[float(v) for v in vals])
+    return arr
+
+
+def sampler_plms_step(eps_model, x, w, coef, cfg, scale, C, old=(None, None, None), noise=None, x_prev=None,
+                      pred_x0=None, e_t_out=None):
+    """eps_model: NHWC UNet output [cfg?2B:B, h, w, ld]; x: fp32 NCHW [B, C, h, w]. See mdx.h for the formulas."""
+    lib = _lib.load()
+    B, Cx, h, wd = x.shape
+    if Cx != C:
+        raise ValueError("channel mismatch")
+    x = _f32(x, "x")
+    if x_prev is None:
+        x_prev = torch.empty_like(x)
+    ld = eps_model.shape[-1]
+    if not eps_model.is_contiguous() or eps_model.shape[0] != (2 * B if cfg else B):
+        raise ValueError("eps_model must be contiguous NHWC with %d images" % (2 * B if cfg else B))
+    check(lib.mdx_sampler_plms_step(_p(eps_model), ld, _dt(eps_model), int(cfg), float(scale), _p(x),
+                                    _p(_f32(old[0], "old1")), _p(_f32(old[1], "old2")), _p(_f32(old[2], "old3")),
+                                    ctypes.cast(_host_floats(w), ctypes.c_void_p),
+                                    ctypes.cast(_host_floats(coef), ctypes.c_void_p), _p(_f32(noise, "noise")),
+                                    _p(x_prev), _p(pred_x0), _p(e_t_out), B, C, h, wd, _stream()),
+          "mdx_sampler_plms_step")
+    return x_prev
+
+
+def sampler_dpmpp2m_step(eps_model, x, coef, cfg, scale, C, model_type=0, x0_prev=None, x_next=None, x0_cur=None):
+    lib = _lib.load()
+    B, Cx, h, wd = x.shape
+    x = _f32(x, "x")
+    if x_next is None:
+        x_next = torch.empty_like(x)
+    if x0_cur is None:
+        x0_cur = torch.empty_like(x)
+    ld = eps_model.shape[-1]
+    if not eps_model.is_contiguous() or eps_model.shape[0] != (2 * B if cfg else B):
+        raise ValueError("eps_model must be contiguous NHWC with %d images" % (2 * B if cfg else B))
+    check(lib.mdx_sampler_dpmpp2m_step(_p(eps_model), ld, _dt(eps_model), int(cfg), float(scale), int(model_type),
+                                       _p(x), _p(_f32(x0_prev, "x0_prev")),
+                                       ctypes.cast(_host_floats(coef), ctypes.c_void_p), _p(x_next), _p(x0_cur), B, C,
+                                       h, wd, _stream()), "mdx_sampler_dpmpp2m_step")
+    return x_next, x0_cur

@@ -1,0 +1,315 @@
+"""Sampler loops with the reference's API, running the UNet and the per-step arithmetic on the GPU kernels.
+
+    sampler = PLMSSampler(model)            # or DPMSolverSampler(model) / DDIMSampler(model)
+    samples, intermediates = sampler.sample(S, batch_size, shape, conditioning, ..., x_T=...,
+                                            unconditional_guidance_scale=..., unconditional_conditioning=..., eta=...)
+
+Signatures, argument meaning, printed warnings and raised errors follow
+vision/stablediffusionv2/ldm/models/diffusion/plms.py:27-248 and dpm_solver/sampler.py:21-92 (wukong-huahua's
+copies are identical for this path).  `DDIMSampler` has no class in the reference: it is the DDIM
+update of `PLMSSampler.get_x_prev_and_pred_x0` (plms.py:210-228) applied with e' = e_t every step, the sampler the
+headline metric names.
+
+Per step the host does: one UNet evaluation (a CUDA-graph replay when enabled) and ONE elementwise kernel
+(classifier-free-guidance combine + latent update, mdx_sampler_*).  The CFG concat of plms.py:192-194 is not
+materialised: the UNet reads the latent batch twice.
+"""
+import numpy as np
+import torch
+
+from . import ops
+
+
+def make_ddim_timesteps(ddim_discr_method="uniform", num_ddim_timesteps=50, num_ddpm_timesteps=1000, verbose=False):
+    """ldm/modules/diffusionmodules/util.py:134-148."""
+    if ddim_discr_method == "uniform":
+        c = num_ddpm_timesteps // num_ddim_timesteps
+        ddim_timesteps = np.asarray(list(range(0, num_ddpm_timesteps, c)))
+    elif ddim_discr_method == "quad":
+        ddim_timesteps = ((np.linspace(0, np.sqrt(num_ddpm_timesteps * .8), num_ddim_timesteps)) ** 2).astype(int)
+    else:
+        raise NotImplementedError('There is no ddim discretization method called "%s"' % ddim_discr_method)
+    steps_out = ddim_timesteps + 1
+    if verbose:
+        print("Selected timesteps for ddim sampler: %s" % steps_out)
+    return steps_out
+
+
+def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta=0.0, verbose=False):
+    """ldm/modules/diffusionmodules/util.py:151-162."""
+    alphacums = np.asarray(alphacums, dtype=np.float32)
+    alphas = alphacums[ddim_timesteps]
+    alphas_prev = np.concatenate((alphacums[:1], alphacums[ddim_timesteps[:-1]]))
+    sigmas = (eta * np.sqrt((1 - alphas_prev) / (1 - alphas) * (1 - alphas / alphas_prev))).astype(np.float32)
+    return sigmas, alphas, alphas_prev
+
+
+def _check_unsupported(mask, x0, score_corrector, quantize_x0, noise_dropout):
+    if mask is not None or x0 is not None:
+        raise NotImplementedError("mask/x0 (inpainting blend, plms.py:156-159) is outside this path's scope")
+    if score_corrector is not None:
+        raise NotImplementedError("score_corrector is not supported")
+    if quantize_x0:
+        raise NotImplementedError("quantize_x0 is not supported")
+    if noise_dropout:
+        raise NotImplementedError("noise_dropout is not supported")
+
+
+def _warn_batch(conditioning, batch_size):
+    if conditioning is not None:  # plms.py:93-100
+        if isinstance(conditioning, dict):
+            cbs = conditioning[list(conditioning.keys())[0]].shape[0]
+        else:
+            cbs = conditioning.shape[0]
+        if cbs != batch_size:
+            print("Warning: Got %d conditionings but batch-size is %d" % (cbs, batch_size))
+
+
+class _GuidedUNet:
+    """Binds (cond, uncond, scale) to the UNet: evaluates the (2B when guided) batch and tells the step kernel
+    whether to combine."""
+
+    def __init__(self, model, cond, uncond, scale):
+        self.unet = model.unet
+        self.cfg = not (uncond is None or scale == 1.0)  # plms.py:189
+        self.scale = float(scale)
+        if isinstance(cond, dict):
+            raise NotImplementedError("dict conditioning (hybrid / inpaint) is outside this path's scope")
+        ctx = torch.cat((uncond, cond), dim=0) if self.cfg else cond  # order of plms.py:194
+        self.unet.set_context(ctx)
+
+    def __call__(self, x, t_value):
+        n = x.shape[0] * (2 if self.cfg else 1)
+        t = torch.full((n,), float(t_value), dtype=torch.float32, device=x.device)
+        return self.unet.forward_nhwc(x, t, repeat=2 if self.cfg else 1)
+
+
+class PLMSSampler(object):
+    ddim = False
+
+    def __init__(self, model, schedule="linear", **kwargs):
+        self.model = model
+        self.ddpm_num_timesteps = model.num_timesteps
+        self.schedule = schedule
+
+    def make_schedule(self, ddim_num_steps, ddim_discretize="uniform", ddim_eta=0., verbose=True):
+        if ddim_eta != 0 and not self.ddim:
+            raise ValueError('ddim_eta must be 0 for PLMS')
+        self.ddim_timesteps = make_ddim_timesteps(ddim_discr_method=ddim_discretize,
+                                                  num_ddim_timesteps=ddim_num_steps,
+                                                  num_ddpm_timesteps=self.ddpm_num_timesteps, verbose=verbose)
+        alphas_cumprod = np.asarray(self.model.alphas_cumprod, dtype=np.float32)
+        assert alphas_cumprod.shape[0] == self.ddpm_num_timesteps, 'alphas have to be defined for each timestep'
+        self.betas = self.model.betas
+        self.alphas_cumprod = alphas_cumprod
+        self.alphas_cumprod_prev = self.model.alphas_cumprod_prev
+        self.sqrt_alphas_cumprod = np.sqrt(alphas_cumprod)
+        self.sqrt_one_minus_alphas_cumprod = np.sqrt(1. - alphas_cumprod)
+        self.log_one_minus_alphas_cumprod = np.log(1. - alphas_cumprod)
+        self.sqrt_recip_alphas_cumprod = np.sqrt(1. / alphas_cumprod)
+        self.sqrt_recipm1_alphas_cumprod = np.sqrt(1. / alphas_cumprod - 1)
+        ddim_sigmas, ddim_alphas, ddim_alphas_prev = make_ddim_sampling_parameters(
+            alphacums=alphas_cumprod, ddim_timesteps=self.ddim_timesteps, eta=ddim_eta, verbose=verbose)
+        self.ddim_sigmas = ddim_sigmas
+        self.ddim_alphas = ddim_alphas
+        self.ddim_alphas_prev = ddim_alphas_prev
+        self.ddim_sqrt_one_minus_alphas = np.sqrt(1. - ddim_alphas)
+
+    def sample(self, S, batch_size, shape, conditioning=None, callback=None, normals_sequence=None,
+               img_callback=None, quantize_x0=False, eta=0., mask=None, x0=None, temperature=1., noise_dropout=0.,
+               score_corrector=None, corrector_kwargs=None, verbose=True, x_T=None, log_every_t=100,
+               unconditional_guidance_scale=1., unconditional_conditioning=None, **kwargs):
+        _warn_batch(conditioning, batch_size)
+        self.make_schedule(ddim_num_steps=S, ddim_eta=eta, verbose=False)
+        C, H, W = shape
+        size = (batch_size, C, H, W)
+        if verbose:
+            print('Data shape for %s sampling is %s' % ("DDIM" if self.ddim else "PLMS", (size,)))
+        return self.plms_sampling(conditioning, size, callback=callback, img_callback=img_callback,
+                                  quantize_denoised=quantize_x0, mask=mask, x0=x0, noise_dropout=noise_dropout,
+                                  temperature=temperature, score_corrector=score_corrector,
+                                  corrector_kwargs=corrector_kwargs, x_T=x_T, log_every_t=log_every_t,
+                                  unconditional_guidance_scale=unconditional_guidance_scale,
+                                  unconditional_conditioning=unconditional_conditioning, verbose=verbose)
+
+    def plms_sampling(self, cond, shape, x_T=None, ddim_use_original_steps=False, callback=None, timesteps=None,
+                      quantize_denoised=False, mask=None, x0=None, img_callback=None, log_every_t=100,
+                      temperature=1., noise_dropout=0., score_corrector=None, corrector_kwargs=None,
+                      unconditional_guidance_scale=1., unconditional_conditioning=None, verbose=True):
+        _check_unsupported(mask, x0, score_corrector, quantize_denoised, noise_dropout)
+        if ddim_use_original_steps or timesteps is not None:
+            raise NotImplementedError("ddim_use_original_steps / explicit timesteps are not used by txt2img")
+        device = self.model.unet.device
+        b, C = shape[0], shape[1]
+        img = torch.randn(shape, device=device, dtype=torch.float32) if x_T is None else \
+            x_T.to(device=device, dtype=torch.float32).contiguous().clone()
+        unet = _GuidedUNet(self.model, cond, unconditional_conditioning, unconditional_guidance_scale)
+        time_range = np.flip(self.ddim_timesteps)
+        total_steps = self.ddim_timesteps.shape[0]
+        if verbose:
+            print("Running %s Sampling with %d timesteps" % ("DDIM" if self.ddim else "PLMS", total_steps))
+        intermediates = {'x_inter': [img], 'pred_x0': [img]}
+        old_eps = []
+        for i, step in enumerate(time_range):
+            index = total_steps - i - 1
+            step_next = time_range[min(i + 1, len(time_range) - 1)]
+            coef = (self.ddim_alphas[index], self.ddim_alphas_prev[index], self.ddim_sigmas[index],
+                    self.ddim_sqrt_one_minus_alphas[index])
+            noise = None
+            if float(self.ddim_sigmas[index]) != 0.0:  # noise_like(...) * temperature, plms.py:222
+                noise = torch.randn(shape, device=device, dtype=torch.float32) * temperature
+            eps_m = unet(img, int(step))
+            e_t = torch.empty_like(img)
+            pred_x0 = torch.empty_like(img)
+            if self.ddim:
+                img = ops.sampler_plms_step(eps_m, img, (1., 0., 0., 0.), coef, unet.cfg, unet.scale, C, noise=noise,
+                                            pred_x0=pred_x0, e_t_out=e_t)
+            elif len(old_eps) == 0:
+                # Pseudo Improved Euler (2nd order), plms.py:231-235: a second UNet evaluation at (x_prev, t_next)
+                x_tmp = ops.sampler_plms_step(eps_m, img, (1., 0., 0., 0.), coef, unet.cfg, unet.scale, C,
+                                              noise=noise, e_t_out=e_t)
+                eps_next = unet(x_tmp, int(step_next))
+                img = ops.sampler_plms_step(eps_next, img, (.5, .5, 0., 0.), coef, unet.cfg, unet.scale, C,
+                                            old=(e_t, None, None), noise=noise, pred_x0=pred_x0)
+            else:
+                if len(old_eps) == 1:  # Adams-Bashforth 2 / 3 / 4, plms.py:236-244
+                    w, old = (3 / 2, -1 / 2, 0., 0.), (old_eps[-1], None, None)
+                elif len(old_eps) == 2:
+                    w, old = (23 / 12, -16 / 12, 5 / 12, 0.), (old_eps[-1], old_eps[-2], None)
+                else:
+                    w, old = (55 / 24, -59 / 24, 37 / 24, -9 / 24), (old_eps[-1], old_eps[-2], old_eps[-3])
+                img = ops.sampler_plms_step(eps_m, img, w, coef, unet.cfg, unet.scale, C, old=old, noise=noise,
+                                            pred_x0=pred_x0, e_t_out=e_t)
+            old_eps.append(e_t)
+            if len(old_eps) >= 4:
+                old_eps.pop(0)
+            if callback:
+                callback(i)
+            if img_callback:
+                img_callback(pred_x0, i)
+            if index % log_every_t == 0 or index == total_steps - 1:
+                intermediates['x_inter'].append(img)
+                intermediates['pred_x0'].append(pred_x0)
+        return img, intermediates
+
+
+class DDIMSampler(PLMSSampler):
+    """DDIM (eta-parameterised) with the PLMSSampler API; see the module docstring."""
+    ddim = True
+
+
+# ----------------------------------------------------------------------------------------------------------
+# DPM-Solver++ (2M)
+# ----------------------------------------------------------------------------------------------------------
+def interpolate_fn(x, xp, yp):
+    """dpm_solver.py:1126-1171 for one channel: piecewise-linear through the key points, outermost segments
+    extended.  The reference finds the segment by sorting concat(x, xp); a binary search gives the same segment
+    (and the same value when x coincides with a key point)."""
+    x = np.atleast_1d(np.asarray(x, dtype=np.float32))
+    K = xp.shape[0]
+    idx = np.searchsorted(xp, x, side="left")
+    s = np.where(idx == 0, 0, np.where(idx == K, K - 2, idx - 1))
+    return (yp[s] + (x - xp[s]) * (yp[s + 1] - yp[s]) / (xp[s + 1] - xp[s])).astype(np.float32)
+
+
+class NoiseScheduleVP:
+    """dpm_solver.py:20-168 for schedule='discrete' (the only one DPMSolverSampler builds, sampler.py:75)."""
+
+    def __init__(self, schedule='discrete', betas=None, alphas_cumprod=None, continuous_beta_0=0.1,
+                 continuous_beta_1=20.):
+        if schedule != 'discrete':
+            raise ValueError("Unsupported noise schedule {}. Only 'discrete' is built by the sampler".format(schedule))
+        if betas is not None:
+            log_alphas = 0.5 * np.cumsum(np.log(1 - np.asarray(betas, dtype=np.float32)))
+        else:
+            assert alphas_cumprod is not None
+            log_alphas = 0.5 * np.log(np.asarray(alphas_cumprod, dtype=np.float32))
+        self.schedule = schedule
+        self.total_N = len(log_alphas)
+        self.T = 1.
+        t = np.linspace(np.float32(0.), np.float32(1.), self.total_N + 1, dtype=np.float32)[1:]
+        self.t_array = t.astype(np.float16).astype(np.float32)  # fp16 cast of dpm_solver.py:100-103
+        self.log_alpha_array = log_alphas.astype(np.float32)
+
+    def marginal_log_mean_coeff(self, t):
+        return interpolate_fn(t, self.t_array, self.log_alpha_array)
+
+    def marginal_alpha(self, t):
+        return np.exp(self.marginal_log_mean_coeff(t))
+
+    def marginal_std(self, t):
+        return np.sqrt(1. - np.exp(2. * self.marginal_log_mean_coeff(t)))
+
+    def marginal_lambda(self, t):
+        log_mean_coeff = self.marginal_log_mean_coeff(t)
+        log_std = 0.5 * np.log(1. - np.exp(2. * log_mean_coeff))
+        return log_mean_coeff - log_std
+
+
+class DPMSolverSampler(object):
+    def __init__(self, model, **kwargs):
+        self.model = model
+        self.register_buffer('alphas_cumprod', model.alphas_cumprod)
+
+    def register_buffer(self, name, attr):
+        setattr(self, name, attr)
+
+    def sample(self, S, batch_size, shape, conditioning=None, callback=None, normals_sequence=None,
+               img_callback=None, quantize_x0=False, eta=0., mask=None, x0=None, temperature=1., noise_dropout=0.,
+               score_corrector=None, corrector_kwargs=None, verbose=True, x_T=None, log_every_t=100,
+               unconditional_guidance_scale=1., unconditional_conditioning=None, **kwargs):
+        _warn_batch(conditioning, batch_size)
+        C, H, W = shape
+        size = (batch_size, C, H, W)
+        device = self.model.unet.device
+        img = torch.randn(size, device=device, dtype=torch.float32) if x_T is None else \
+            x_T.to(device=device, dtype=torch.float32).contiguous().clone()
+        ns = NoiseScheduleVP('discrete', alphas_cumprod=self.alphas_cumprod)
+        # sampler.py:77-85 hard-codes model_type="noise"; "v" (dpm_solver.py:281-284) is selected by the model's
+        # parameterization so that the 768-v configuration runs through the same wrapper arithmetic.
+        model_type = 1 if getattr(self.model, "parameterization", "eps") == "v" else 0
+        unet = _GuidedUNet(self.model, conditioning, unconditional_conditioning, unconditional_guidance_scale)
+        order, steps = 2, S
+        if steps < order:
+            raise AssertionError("steps >= order")  # dpm_solver.py:1064
+        t_0, t_T = 1. / ns.total_N, ns.T
+        # get_time_steps('time_uniform'): fp32 linspace cast to fp16 (dpm_solver.py:414-415)
+        timesteps = np.linspace(np.float32(t_T), np.float32(t_0), steps + 1, dtype=np.float32).astype(np.float16)
+        x = img
+        x0_prev = None
+        for i in range(steps):
+            s16 = timesteps[i]
+            # get_model_input_time on the fp16 tensor: (t - 1/N) * 1000 (dpm_solver.py:256-265)
+            t_input = np.float32((s16 - np.float16(1. / ns.total_N)) * np.float16(1000.))
+            s = np.float32(s16)
+            t = np.float32(timesteps[i + 1])
+            alpha_s, sigma_s = ns.marginal_alpha(s)[0], ns.marginal_std(s)[0]
+            lam_s, lam_t = ns.marginal_lambda(s)[0], ns.marginal_lambda(t)[0]
+            h = lam_t - lam_s
+            sigma_t = ns.marginal_std(t)[0]
+            alpha_t = np.exp(ns.marginal_log_mean_coeff(t)[0])
+            step = i + 1  # index of the time we move to, as in the loop of dpm_solver.py:1073-1094
+            if step == 1:
+                step_order = 1
+            elif steps < 15:  # lower_order_final
+                step_order = min(order, steps + 1 - step)
+            else:
+                step_order = order
+            if step_order == 1 or x0_prev is None:
+                # dpm_solver_first_update, predict_x0 branch (dpm_solver.py:504-513)
+                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -alpha_t * np.expm1(-h), 0.)
+                x0p = None
+            else:
+                # multistep_dpm_solver_second_update, 'dpm_solver' type (dpm_solver.py:756-777)
+                lam_p1 = ns.marginal_lambda(np.float32(timesteps[i - 1]))[0]
+                h_0 = lam_s - lam_p1
+                r0 = h_0 / h
+                c = alpha_t * (np.exp(-h) - 1.)
+                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -c, -0.5 * c / r0)
+                x0p = x0_prev
+            out = unet(x, float(t_input))
+            x, x0_prev = ops.sampler_dpmpp2m_step(out, x, coef, unet.cfg, unet.scale, C, model_type=model_type,
+                                                  x0_prev=x0p)
+            if callback:
+                callback(i)
+        return x, None

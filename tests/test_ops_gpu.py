@@ -1,0 +1,292 @@
+"""Kernel-level parity (-m gpu): every C-ABI operator against a plain torch fp32 CPU restatement of the
+reference op it replaces, on seeded inputs.  bf16 kernels are compared on bf16-rounded inputs, so the only
+differences are accumulation order and the final rounding: tolerance 2e-2 of the output's max magnitude for
+bf16 outputs (north star: <= 1e-2 per UNet eps; single ops are looser-bounded but far tighter in practice),
+1e-4 for the fp32 check-mode kernels."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from minddiffusion_b200 import ops
+    return ops
+
+
+def rel_err(a, b):
+    a = a.detach().float().cpu()
+    b = b.detach().float().cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def bf(x):
+    return x.to(torch.bfloat16).float()
+
+
+def conv_ref(x_nhwc, w_oihw, b=None, stride=1, pad=1):
+    y = F.conv2d(x_nhwc.permute(0, 3, 1, 2), w_oihw, b, stride=stride, padding=pad)
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+def pack_k(w_oihw):
+    return w_oihw.permute(0, 2, 3, 1).reshape(w_oihw.shape[0], -1).contiguous()
+
+
+# ------------------------------------------------------------------ tcgen05 implicit GEMM
+@pytest.mark.parametrize("M,K,N", [(128, 64, 64), (256, 320, 320), (1000, 1024, 640), (77 * 2, 128, 256),
+                                   (4096, 1280, 960), (130, 64, 16)])
+def test_gemm_tc_dense(M, K, N):
+    ops = _ops()
+    g = torch.Generator().manual_seed(M + K + N)
+    a = bf(torch.randn(M, K, generator=g))
+    w = bf(torch.randn(N, K, generator=g) / K ** 0.5)
+    bias = torch.randn(N, generator=g)
+    res = bf(torch.randn(M, N, generator=g))
+    ref = a @ w.t() + bias + res
+    out = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), bias=bias.cuda(), residual=res.cuda().bfloat16())
+    assert rel_err(out, ref) < 1e-2
+    out32 = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), out_dtype=torch.float32)
+    assert rel_err(out32, a @ w.t()) < 1e-4
+
+
+@pytest.mark.parametrize("bn", [64, 128, 160, 256])
+def test_gemm_tc_block_n_variants(bn):
+    ops = _ops()
+    g = torch.Generator().manual_seed(bn)
+    M, K, N = 700, 448, 640
+    a = bf(torch.randn(M, K, generator=g))
+    w = bf(torch.randn(N, K, generator=g) / K ** 0.5)
+    out = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), out_dtype=torch.float32, block_n=bn)
+    assert rel_err(out, a @ w.t()) < 1e-4
+
+
+@pytest.mark.parametrize("n,H,W,Cin,Cout", [(2, 8, 8, 64, 64), (1, 16, 16, 128, 320), (3, 32, 32, 64, 160),
+                                            (2, 64, 64, 64, 64), (1, 12, 12, 64, 128), (2, 96, 96, 64, 64),
+                                            (5, 4, 4, 128, 64)])
+def test_gemm_tc_conv3x3(n, H, W, Cin, Cout):
+    ops = _ops()
+    g = torch.Generator().manual_seed(n * H + Cin + Cout)
+    x = bf(torch.randn(n, H, W, Cin, generator=g))
+    w = bf(torch.randn(Cout, Cin, 3, 3, generator=g) / (9 * Cin) ** 0.5)
+    b = torch.randn(Cout, generator=g)
+    rb = torch.randn(n, Cout + 64, generator=g)  # per-image emb add read through a strided view
+    ref = conv_ref(x, w, b) + rb[:, None, None, 32:32 + Cout]
+    out = ops.gemm_tc([(x.cuda().bfloat16(), 9)], pack_k(w).cuda().bfloat16(), bias=b.cuda(),
+                      rowbias=rb.cuda()[:, 32:32 + Cout])
+    assert rel_err(out.view(n, H, W, Cout), ref) < 1e-2
+
+
+def test_gemm_tc_conv_with_fused_skip():
+    """ResBlock tail: conv3x3(h) + conv1x1(concat(x1, x2)) accumulated in one TMEM tile (K-concatenation)."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(7)
+    n, H, W, C, C1, C2 = 2, 16, 16, 128, 128, 64
+    h = bf(torch.randn(n, H, W, C, generator=g))
+    x1 = bf(torch.randn(n, H, W, C1, generator=g))
+    x2 = bf(torch.randn(n, H, W, C2, generator=g))
+    w2 = bf(torch.randn(C, C, 3, 3, generator=g) / (9 * C) ** 0.5)
+    ws = bf(torch.randn(C, C1 + C2, 1, 1, generator=g) / (C1 + C2) ** 0.5)
+    b = torch.randn(C, generator=g)
+    ref = conv_ref(h, w2, b) + conv_ref(torch.cat((x1, x2), -1), ws, None, pad=0)
+    wk = torch.cat((pack_k(w2), ws.reshape(C, C1 + C2)), dim=1)
+    out = ops.gemm_tc([(h.cuda().bfloat16(), 9), (x1.cuda().bfloat16(), 1), (x2.cuda().bfloat16(), 1)],
+                      wk.cuda().bfloat16(), bias=b.cuda())
+    assert rel_err(out.view(n, H, W, C), ref) < 1e-2
+
+
+def test_gemm_tc_geglu():
+    from minddiffusion_b200.unet import pack_geglu
+    ops = _ops()
+    g = torch.Generator().manual_seed(11)
+    M, C = 300, 320
+    a = bf(torch.randn(M, C, generator=g))
+    w = bf(torch.randn(8 * C, C, generator=g) / C ** 0.5)
+    b = torch.randn(8 * C, generator=g)
+    proj = a @ w.t() + b
+    val, gate = proj.chunk(2, dim=-1)
+    ref = val * F.gelu(gate, approximate="tanh")
+    wp, bp, bn = pack_geglu(w.cuda(), b.cuda())
+    out = ops.gemm_tc([(a.cuda().bfloat16(), 1)], wp.bfloat16(), bias=bp, geglu=True, block_n=bn)
+    assert out.shape == (M, 4 * C)
+    assert rel_err(out, ref) < 1e-2
+
+
+def test_gemm_tc_strided_views():
+    """A operand and output as channel slices of wider buffers (how q/k/v and fused projections are addressed)."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(13)
+    M, K, N = 512, 128, 64
+    wide = bf(torch.randn(M, 3 * K, generator=g))
+    w = bf(torch.randn(N, K, generator=g) / K ** 0.5)
+    a = wide[:, K:2 * K]
+    dst = torch.zeros(M, 2 * N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm_tc([(wide.cuda().bfloat16()[:, K:2 * K], 1)], w.cuda().bfloat16(), out=dst[:, N:])
+    assert rel_err(dst[:, N:], a @ w.t()) < 1e-2
+    assert float(dst[:, :N].abs().max()) == 0.0
+
+
+def test_gemm_tc_rejects_bad_arguments():
+    from minddiffusion_b200._lib import MdxError
+    ops = _ops()
+    a = torch.zeros(128, 48, dtype=torch.bfloat16, device="cuda")  # K not a multiple of 64
+    w = torch.zeros(64, 48, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(MdxError):
+        ops.gemm_tc([(a, 1)], w)
+
+
+# ------------------------------------------------------------------ CUDA-core conv / dense
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("stride,upsample,k,cin,cout", [(1, False, 3, 4, 64), (2, False, 3, 32, 48),
+                                                        (1, True, 3, 16, 20), (1, False, 1, 40, 24)])
+def test_conv_direct(dtype, tol, stride, upsample, k, cin, cout):
+    ops = _ops()
+    g = torch.Generator().manual_seed(cin * cout + stride)
+    n, H, W = 2, 10, 12
+    x = torch.randn(n, H, W, cin, generator=g)
+    w = torch.randn(cout, cin, k, k, generator=g) / (k * k * cin) ** 0.5
+    b = torch.randn(cout, generator=g)
+    if dtype == torch.bfloat16:
+        x, w = bf(x), bf(w)
+    xr = x.permute(0, 3, 1, 2)
+    if upsample:
+        xr = F.interpolate(xr, scale_factor=2, mode="nearest")
+    ref = F.conv2d(xr, w, b, stride=stride, padding=k // 2).permute(0, 2, 3, 1)
+    out = ops.conv_direct(x.cuda().to(dtype), pack_k(w).cuda().to(dtype), k, k, stride, k // 2, upsample=upsample,
+                          bias=b.cuda())
+    assert tuple(out.shape) == tuple(ref.shape)
+    assert rel_err(out, ref) < tol
+
+
+def test_conv_direct_pre_silu_dense():
+    ops = _ops()
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(6, 1280, generator=g)
+    w = torch.randn(320, 1280, generator=g) / 1280 ** 0.5
+    b = torch.randn(320, generator=g)
+    ref = F.linear(F.silu(x), w, b)
+    out = ops.conv_direct(x.cuda(), w.cuda(), bias=b.cuda(), pre_silu=True)
+    assert rel_err(out, ref) < 1e-4
+
+
+# ------------------------------------------------------------------ norms
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("C1,C2,HW,silu,eps", [(320, 0, 64, True, 1e-5), (640, 320, 256, True, 1e-5),
+                                               (1280, 640, 16, False, 1e-6), (64, 0, 1024, True, 1e-5),
+                                               (1280, 1280, 64, True, 1e-5), (192, 0, 100, False, 1e-5)])
+def test_groupnorm(dtype, tol, C1, C2, HW, silu, eps):
+    ops = _ops()
+    g = torch.Generator().manual_seed(C1 + C2 + HW)
+    n = 3
+    x1 = torch.randn(n, HW, 1, C1, generator=g) * 1.5 + 0.3
+    x2 = torch.randn(n, HW, 1, C2, generator=g) if C2 else None
+    gamma = 1 + 0.1 * torch.randn(C1 + C2, generator=g)
+    beta = 0.1 * torch.randn(C1 + C2, generator=g)
+    if dtype == torch.bfloat16:
+        x1 = bf(x1)
+        x2 = bf(x2) if x2 is not None else None
+    xc = torch.cat((x1, x2), -1) if x2 is not None else x1
+    ref = F.group_norm(xc.permute(0, 3, 1, 2), 32, gamma, beta, eps).permute(0, 2, 3, 1)
+    if silu:
+        ref = F.silu(ref)
+    out = ops.groupnorm(x1.cuda().to(dtype), gamma.cuda(), beta.cuda(), 32, eps, silu=silu,
+                        x2=x2.cuda().to(dtype) if x2 is not None else None)
+    assert rel_err(out, ref) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("C", [64, 320, 640, 1280, 1024])
+def test_layernorm(dtype, tol, C):
+    ops = _ops()
+    g = torch.Generator().manual_seed(C)
+    x = torch.randn(37, C, generator=g) * 2 + 0.5
+    gamma = 1 + 0.1 * torch.randn(C, generator=g)
+    beta = 0.1 * torch.randn(C, generator=g)
+    if dtype == torch.bfloat16:
+        x = bf(x)
+    ref = F.layer_norm(x, (C,), gamma, beta, 1e-5)
+    out = ops.layernorm(x.cuda().to(dtype), gamma.cuda(), beta.cuda(), 1e-5)
+    assert rel_err(out, ref) < tol
+
+
+# ------------------------------------------------------------------ attention
+def attn_ref(q, k, v, heads, scale):
+    B, Nq, C = q.shape
+    d = C // heads
+
+    def sp(t):
+        return t.reshape(B, t.shape[1], heads, d).permute(0, 2, 1, 3)
+
+    s = torch.matmul(sp(q), sp(k).transpose(-1, -2)) * scale
+    o = torch.matmul(torch.softmax(s, -1), sp(v))
+    return o.permute(0, 2, 1, 3).reshape(B, Nq, C)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("B,heads,Nq,Nk,d", [(2, 5, 256, 256, 64), (1, 2, 1024, 77, 64), (2, 8, 200, 77, 40),
+                                             (1, 8, 64, 64, 80), (1, 4, 130, 130, 160), (1, 1, 4096, 4096, 64),
+                                             (2, 8, 64, 77, 8), (1, 8, 100, 50, 16), (1, 8, 96, 96, 32)])
+def test_attention(dtype, tol, B, heads, Nq, Nk, d):
+    ops = _ops()
+    g = torch.Generator().manual_seed(B * heads + Nq + d)
+    C = heads * d
+    q = torch.randn(B, Nq, C, generator=g)
+    kv = torch.randn(B, Nk, 2 * C, generator=g)  # k and v as slices of one fused projection buffer
+    if dtype == torch.bfloat16:
+        q, kv = bf(q), bf(kv)
+    scale = d ** -0.5
+    ref = attn_ref(q, kv[:, :, :C], kv[:, :, C:], heads, scale)
+    kvd = kv.cuda().to(dtype)
+    out = ops.attention(q.cuda().to(dtype), kvd[:, :, :C], kvd[:, :, C:], heads, scale)
+    assert rel_err(out, ref) < tol
+
+
+# ------------------------------------------------------------------ movers and small kernels
+def test_timestep_embedding():
+    import math
+    ops = _ops()
+    t = torch.tensor([1.0, 501.0, 981.0, 999.0234], dtype=torch.float32)
+    half = 160
+    freqs = torch.exp(-math.log(10000) * torch.arange(0, half, dtype=torch.float32) / half)
+    args = t[:, None] * freqs[None]
+    ref = torch.cat((torch.cos(args), torch.sin(args)), -1)
+    out = ops.timestep_embedding(t.cuda(), 320)
+    assert float((out.cpu() - ref).abs().max()) < 2e-4  # fp32 sin/cos of arguments up to 1e3
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_layout_movers(dtype):
+    ops = _ops()
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 4, 6, 5, generator=g)
+    out = ops.nchw_to_nhwc(x.cuda(), dtype, repeat=2, cpad=8)
+    ref = torch.zeros(4, 6, 5, 8)
+    ref[:, :, :, :4] = torch.cat((x, x), 0).permute(0, 2, 3, 1)
+    assert rel_err(out, ref.to(dtype)) < 1e-6 and tuple(out.shape) == (4, 6, 5, 8)
+    back = ops.nhwc_to_nchw(out, 4)
+    assert rel_err(back, torch.cat((x, x), 0).to(dtype)) < 1e-6
+    y = torch.randn(2, 3, 4, 16, generator=g).to(dtype)
+    up = ops.upsample_nearest2x(y.cuda())
+    assert torch.equal(up.cpu(), F.interpolate(y.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest")
+                       .permute(0, 2, 3, 1).to(dtype))
+    a, b = torch.randn(7, 16, generator=g).to(dtype), torch.randn(7, 8, generator=g).to(dtype)
+    assert torch.equal(ops.concat_channels(a.cuda(), b.cuda()).cpu(), torch.cat((a, b), -1))
+    z = torch.randn(2, 8, 8, 16, generator=g).to(dtype)
+    col = ops.im2col3x3(z.cuda(), 2)
+    unf = F.unfold(z.float().permute(0, 3, 1, 2), 3, padding=1, stride=2)  # [n, C*9, L], order (c, r, s)
+    unf = unf.view(2, 16, 9, 4, 4).permute(0, 3, 4, 2, 1).reshape(2, 4, 4, 9 * 16)
+    assert torch.equal(col.cpu().float(), unf)
+    assert torch.equal(ops.cast(z.cuda(), torch.float32).cpu(), z.float())
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+def test_geglu_kernel(dtype, tol):
+    ops = _ops()
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(33, 256, generator=g)
+    if dtype == torch.bfloat16:
+        x = bf(x)
+    ref = x[:, :128] * F.gelu(x[:, 128:], approximate="tanh")
+    assert rel_err(ops.geglu(x.cuda().to(dtype)), ref) < tol

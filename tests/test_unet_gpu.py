@@ -1,0 +1,187 @@
+"""UNet and sampler parity (-m gpu): the CUDA path, called through the reference-shaped Python API, against the
+oracle (oracle/sd_unet.py, oracle/samplers.py) on identical seeded weights, x_T and context.
+
+Tolerances (BASELINE.json north_star): per-evaluation eps max|diff|/max|eps| <= 1e-2 in bf16 and <= 1e-4 in the
+fp32 check mode; final latents cosine >= 0.999."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import TINY_UNET, TINY_UNET_V1
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def cosine(a, b):
+    a, b = a.detach().float().cpu().flatten(), b.detach().float().cpu().flatten()
+    return float(torch.dot(a, b) / (a.norm() * b.norm()))
+
+
+def build(cfg, dtype, seed=0):
+    from minddiffusion_b200.unet import UNetModel
+    from minddiffusion_b200.weights import random_unet_params
+    P = random_unet_params(cfg, seed)
+    return UNetModel(P, dtype=dtype, **cfg), {k: torch.from_numpy(v) for k, v in P.items()}
+
+
+def inputs(cfg, B, hw, L=77, seed=1):
+    rs = np.random.RandomState(seed)
+    x = torch.from_numpy(rs.randn(B, cfg["in_channels"], hw, hw).astype(np.float32))
+    ctx = torch.from_numpy(rs.randn(B, L, cfg["context_dim"]).astype(np.float32))
+    return x, ctx
+
+
+@pytest.mark.parametrize("cfg", [TINY_UNET, TINY_UNET_V1], ids=["sd2-shape", "sd-v1-shape"])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)], ids=["fp32", "bf16"])
+def test_tiny_unet_eps(cfg, dtype, tol):
+    from oracle import sd_unet
+    model, Pt = build(cfg, dtype)
+    x, ctx = inputs(cfg, 2, 16)
+    t = torch.tensor([981.0, 21.0])
+    taps_ref, taps = {}, {}
+    ref = sd_unet.unet_forward(Pt, cfg, x, t, ctx, taps=taps_ref)
+    model.set_context(ctx.cuda())
+    out = model.forward_nhwc(x.cuda(), t.cuda(), taps=taps)
+    torch.cuda.synchronize()
+    worst = {k: rel_err(taps[k].permute(0, 3, 1, 2), taps_ref[k]) for k in taps_ref}
+    eps = out[..., :cfg["out_channels"]].permute(0, 3, 1, 2)
+    e = rel_err(eps, ref)
+    assert e < tol, "eps rel err %.3e; per-block %s" % (e, worst)
+    # reference call signature: NCHW in, NCHW out, context passed per call
+    out2 = model(x.cuda(), t.cuda(), context=ctx.cuda())
+    assert rel_err(out2, ref) < tol
+
+
+def test_tiny_unet_odd_shapes_bf16():
+    """Non-square 8x24 latents (tiles that do not cover 128 pixels evenly, down to 1x3), batch 3, short context
+    (ragged K/V tile)."""
+    from oracle import sd_unet
+    model, Pt = build(TINY_UNET, torch.bfloat16, seed=3)
+    rs = np.random.RandomState(4)
+    x = torch.from_numpy(rs.randn(3, 4, 8, 24).astype(np.float32))
+    ctx = torch.from_numpy(rs.randn(3, 10, TINY_UNET["context_dim"]).astype(np.float32))
+    t = torch.tensor([500.0, 1.0, 999.0])
+    ref = sd_unet.unet_forward(Pt, TINY_UNET, x, t, ctx)
+    model.set_context(ctx.cuda())
+    out = model.forward_nhwc(x.cuda(), t.cuda())
+    assert rel_err(out[..., :4].permute(0, 3, 1, 2), ref) < 1e-2
+
+
+def test_cfg_repeat_and_cuda_graph_match_eager():
+    model, _ = build(TINY_UNET, torch.bfloat16)
+    x, ctx = inputs(TINY_UNET, 2, 16)
+    ctx2 = torch.cat((ctx * 0.5, ctx), 0).cuda()
+    model.set_context(ctx2)
+    t = torch.full((4,), 321.0).cuda()
+    eager = model.forward_nhwc(x.cuda(), t, repeat=2).clone()
+    explicit = model.forward_nhwc(torch.cat((x, x), 0).cuda(), t, repeat=1)
+    assert torch.equal(eager, explicit)
+    model.use_cuda_graph = True
+    g1 = model.forward_nhwc(x.cuda(), t, repeat=2).clone()
+    g2 = model.forward_nhwc(x.cuda(), t, repeat=2).clone()
+    assert torch.equal(g1, eager) and torch.equal(g2, eager)
+    # new context of the same shape refills the captured buffers
+    model.set_context(torch.cat((ctx, ctx), 0).cuda())
+    g3 = model.forward_nhwc(x.cuda(), t, repeat=2)
+    model.use_cuda_graph = False
+    e3 = model.forward_nhwc(x.cuda(), t, repeat=2)
+    assert torch.equal(g3, e3) and not torch.equal(g3, eager)
+
+
+def _ldm(model, **kw):
+    from minddiffusion_b200.ldm import LatentDiffusion
+    return LatentDiffusion(model, timesteps=1000, linear_start=0.00085, linear_end=0.012, **kw)
+
+
+def _oracle_model_fn(Pt, cfg):
+    from oracle import sd_unet
+    return lambda x, t, c: sd_unet.unet_forward(Pt, cfg, x, t.to(torch.float32), c)
+
+
+@pytest.mark.parametrize("dtype,eps_tol", [(torch.float32, 2e-4), (torch.bfloat16, 1e-2)], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("which", ["plms", "ddim", "dpm"])
+def test_tiny_sampler_loops(which, dtype, eps_tol):
+    from minddiffusion_b200 import samplers
+    from oracle import samplers as osamp
+    cfg = TINY_UNET
+    model, Pt = build(cfg, dtype)
+    ldm = _ldm(model)
+    x_T, c = inputs(cfg, 2, 16, seed=42)
+    uc = torch.from_numpy(np.random.RandomState(44).randn(*c.shape).astype(np.float32))
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    assert np.array_equal(sched["alphas_cumprod"], ldm.alphas_cumprod)
+    S, scale = 6, 7.5
+    fn = _oracle_model_fn(Pt, cfg)
+    if which == "dpm":
+        ref = osamp.dpmpp2m_sample(fn, sched, S, x_T, c, uc, scale)
+        out, _ = samplers.DPMSolverSampler(ldm).sample(S, 2, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False,
+                                                       unconditional_guidance_scale=scale,
+                                                       unconditional_conditioning=uc.cuda())
+    else:
+        ref, inter_ref = osamp.plms_sample(fn, sched, S, x_T, c, uc, scale, ddim=(which == "ddim"))
+        cls = samplers.DDIMSampler if which == "ddim" else samplers.PLMSSampler
+        out, inter = cls(ldm).sample(S, 2, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False,
+                                     unconditional_guidance_scale=scale, unconditional_conditioning=uc.cuda())
+        assert len(inter["x_inter"]) == len(inter_ref["x_inter"])
+    assert cosine(out, ref) >= 0.999
+    assert rel_err(out, ref) < 10 * eps_tol  # error compounds over S guided steps
+
+
+def test_sampler_api_errors_and_v_prediction():
+    from minddiffusion_b200 import samplers
+    from oracle import samplers as osamp
+    cfg = TINY_UNET
+    model, Pt = build(cfg, torch.float32)
+    ldm = _ldm(model)
+    x_T, c = inputs(cfg, 1, 16, seed=5)
+    with pytest.raises(ValueError, match="ddim_eta must be 0 for PLMS"):
+        samplers.PLMSSampler(ldm).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), eta=0.5, verbose=False)
+    with pytest.raises(NotImplementedError):
+        samplers.PLMSSampler(ldm).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), mask=x_T, x0=x_T, verbose=False)
+    # unguided path (scale 1): batch is NOT doubled (plms.py:189-190)
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    fn = _oracle_model_fn(Pt, cfg)
+    ref, _ = osamp.plms_sample(fn, sched, 3, x_T, c, None, 1.0)
+    out, _ = samplers.PLMSSampler(ldm).sample(3, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False)
+    assert rel_err(out, ref) < 1e-3
+    # v-prediction through the DPM-Solver wrapper (BASELINE config #4's parameterisation)
+    ldm_v = _ldm(model, parameterization="v")
+    refv = osamp.dpmpp2m_sample(fn, sched, 5, x_T, c, None, 1.0, model_type="v")
+    outv, _ = samplers.DPMSolverSampler(ldm_v).sample(5, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False)
+    assert rel_err(outv, refv) < 1e-3
+    # DDIM with eta > 0 draws noise: finite, and different from eta = 0
+    o0, _ = samplers.DDIMSampler(ldm).sample(3, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False)
+    o1, _ = samplers.DDIMSampler(ldm).sample(3, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), eta=1.0, verbose=False)
+    assert torch.isfinite(o1).all() and not torch.equal(o0, o1)
+
+
+def test_sd2_config1_two_step_plms_bf16():
+    """BASELINE config #1: SD2 UNet (v2-inference.yaml), random init, 32x32 latent, batch 1, 2-step PLMS with CFG
+    (3 UNet evaluations at batch 2).  Per-evaluation eps and final latents against the oracle."""
+    from minddiffusion_b200 import samplers
+    from oracle import samplers as osamp
+    from oracle import sd_unet
+    cfg = sd_unet.SD2_UNET
+    model, Pt = build(cfg, torch.bfloat16)
+    ldm = _ldm(model)
+    rs = np.random.RandomState(42)
+    x_T = torch.from_numpy(rs.randn(1, 4, 32, 32).astype(np.float32))
+    c = torch.from_numpy(np.random.RandomState(43).randn(1, 77, 1024).astype(np.float32))
+    uc = torch.from_numpy(np.random.RandomState(44).randn(1, 77, 1024).astype(np.float32))
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    rec = []
+    ref, _ = osamp.plms_sample(_oracle_model_fn(Pt, cfg), sched, 2, x_T, c, uc, 7.5, record=rec)
+    assert len(rec) == 3
+    # first evaluation: identical inputs on both sides -> the per-step eps criterion
+    model.set_context(torch.cat((uc, c), 0).cuda())
+    out = model.forward_nhwc(x_T.cuda(), torch.full((2,), 501.0).cuda(), repeat=2)[..., :4].permute(0, 3, 1, 2)
+    e = out[:1] + 7.5 * (out[1:] - out[:1])
+    assert rel_err(e, rec[0]) <= 1e-2
+    got, _ = samplers.PLMSSampler(ldm).sample(2, 1, (4, 32, 32), c.cuda(), x_T=x_T.cuda(), verbose=False,
+                                              unconditional_guidance_scale=7.5, unconditional_conditioning=uc.cuda())
+    assert cosine(got, ref) >= 0.999
