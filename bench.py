@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""Headline benchmark: images/sec @512x512, 50-step DDIM, CFG 7.5, stablediffusionv2 512-base UNet (BASELINE.json
+configs[2]: batch 64 per GPU, the configuration the metric is quoted on; it fits one B200).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one pass of the hot path over one batch: `DDIMSampler.sample(S=50, batch_size=64, ...)` — 50 guided UNet
+evaluations (CFG batch 128) and 50 fused combine+update kernels.  Synthetic prompts embeddings / latents and seeded
+random-init weights (no checkpoints ship with the reference).
+
+  value : whole-job images/sec with x_T and the conditioning already resident in HBM (CUDA events, max over ranks)
+  e2e   : the same through the public sampler API starting from pinned HOST buffers, H2D of x_T / c / uc and D2H
+          of the latents inside the timed region
+  roofline : the dominant kernel (tcgen05 implicit GEMM, mdx_gemm_tc): sum of algorithmic FLOPs over every launch
+          of one UNet evaluation / sum of their CUDA-event durations, measured live right after the timed region
+  cpu_baseline : the oracle (torch fp32 restatement of the reference; MindSpore is not installable here) on the host
+          cores for a bounded sample of the same workload
+`--impl reference` times that CPU oracle as the reference arm (rank 0 only).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_SAMPLE_FWD_SD2_64 = 804.3e9  # SURVEY.md §3.4 / BASELINE.md §3 (2*MAC), per sample per UNet forward
+
+SD2_UNET = dict(in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],
+                num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_head_channels=64, num_heads=-1,
+                use_spatial_transformer=True, use_linear_in_transformer=True, transformer_depth=1,
+                context_dim=1024, legacy=False)  # configs/v2-inference.yaml:21-37
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    # overrides for development runs; the defaults ARE the named workload
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--sampler-steps", type=int, default=50)
+    ap.add_argument("--latent", type=int, default=64)
+    ap.add_argument("--scale", type=float, default=7.5)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "stablediffusionv2 512-base UNet, batch %d/GPU, %d-step DDIM, CFG %.1f, %dx%d latent" % (
+        a.batch, a.sampler_steps, a.scale, a.latent, a.latent)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle on the host cores, bounded sample
+# ----------------------------------------------------------------------------------------------------------
+def cpu_sample_seconds(a, repeats=1):
+    """One guided UNet evaluation for ONE image (CFG batch 2, latent a.latent^2) + the DDIM update, torch fp32 on
+    all host threads.  Returns (seconds per sample, cores)."""
+    import numpy as np
+    import torch
+    from minddiffusion_b200.weights import random_unet_params
+    from oracle import samplers as osamp
+    from oracle import sd_unet
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    P = {k: torch.from_numpy(v) for k, v in random_unet_params(SD2_UNET, 0).items()}
+    rs = np.random.RandomState(42)
+    x = torch.from_numpy(rs.randn(1, 4, a.latent, a.latent).astype(np.float32))
+    c = torch.from_numpy(np.random.RandomState(43).randn(1, 77, 1024).astype(np.float32))
+    uc = torch.from_numpy(np.random.RandomState(44).randn(1, 77, 1024).astype(np.float32))
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    fn = lambda xx, t, cc: sd_unet.unet_forward(P, SD2_UNET, xx, t.to(torch.float32), cc)
+    times = []
+    with torch.no_grad():
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            # one DDIM step of the 50-step schedule == plms_sample(ddim=True) restricted to its first step
+            e = osamp._cfg_model_output(fn, x, torch.full((1,), 981, dtype=torch.int64), c, uc, a.scale)
+            ac = sched["alphas_cumprod"]
+            a_t, a_prev = float(ac[981]), float(ac[961])
+            x0 = (x - (1 - a_t) ** 0.5 * e) / a_t ** 0.5
+            x = a_prev ** 0.5 * x0 + (1 - a_prev) ** 0.5 * e
+            times.append(time.perf_counter() - t0)
+    return times, cores
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    for _ in range(a.warmup):
+        cpu_sample_seconds(a, 1)
+    times, cores = cpu_sample_seconds(a, a.steps)
+    per_eval = sum(times) / len(times)
+    ips = 1.0 / (a.sampler_steps * per_eval)
+    sample = ("1 image, 1 of %d DDIM steps per bench step (one CFG UNet evaluation at batch 2 + update), "
+              "images/sec extrapolated x%d" % (a.sampler_steps, a.sampler_steps))
+    line = {
+        "impl": "reference", "metric": "images/sec @512^2 50-step DDIM CFG7.5", "value": ips, "unit": "images/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": per_eval * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "executor": "CPU restatement (torch fp32 oracle), not MindSpore"},
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_b200(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from minddiffusion_b200 import _lib, ops, samplers
+    from minddiffusion_b200.ldm import LatentDiffusion
+    from minddiffusion_b200.unet import UNetModel
+    from minddiffusion_b200.weights import random_unet_params
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    P = random_unet_params(SD2_UNET, 0)
+    unet = UNetModel(P, dtype=torch.bfloat16, device=dev, **SD2_UNET)
+    del P
+    unet.use_cuda_graph = not a.no_graph
+    ldm = LatentDiffusion(unet, timesteps=1000, linear_start=0.00085, linear_end=0.012, scale_factor=0.18215)
+    sampler = samplers.DDIMSampler(ldm)
+
+    B, S, h = a.batch, a.sampler_steps, a.latent
+    shape = (4, h, h)
+    # synthetic inputs of the reference shapes: x_T seed 42 (+rank), c / uc seeds 43 / 44
+    x_host = torch.from_numpy(np.random.RandomState(42 + rank).randn(B, *shape).astype(np.float32)).pin_memory()
+    c_host = torch.from_numpy(np.random.RandomState(43).randn(B, 77, 1024).astype(np.float32)).pin_memory()
+    uc_host = torch.from_numpy(np.random.RandomState(44).randn(B, 77, 1024).astype(np.float32)).pin_memory()
+    out_host = torch.empty((B, *shape), dtype=torch.float32).pin_memory()
+    x_dev, c_dev, uc_dev = x_host.to(dev), c_host.to(dev), uc_host.to(dev)
+
+    def step_resident():
+        return sampler.sample(S, B, shape, c_dev, x_T=x_dev, verbose=False, unconditional_guidance_scale=a.scale,
+                              unconditional_conditioning=uc_dev, eta=0.0)[0]
+
+    def step_e2e():
+        xs = x_host.to(dev, non_blocking=True)
+        cs = c_host.to(dev, non_blocking=True)
+        us = uc_host.to(dev, non_blocking=True)
+        out = sampler.sample(S, B, shape, cs, x_T=xs, verbose=False, unconditional_guidance_scale=a.scale,
+                             unconditional_conditioning=us, eta=0.0)[0]
+        out_host.copy_(out, non_blocking=True)
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(a.warmup, 1)):
+        step_resident()
+    launches0 = _lib.launch_count() + unet.replayed_launches
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms = timed(step_resident, a.steps)
+    launches = _lib.launch_count() + unet.replayed_launches - launches0
+    ms_e2e = timed(step_e2e, a.steps)
+    clk = clocks.stop() if rank == 0 else None
+
+    images = B * world * a.steps
+    value = images / (ms / 1e3)
+    e2e = images / (ms_e2e / 1e3)
+
+    # ---- dominant kernel, live: every mdx_gemm_tc launch of one guided UNet evaluation ----
+    prof = []
+    ops.GEMM_TC_PROFILE = prof
+    unet.use_cuda_graph = False
+    t_probe = torch.full((2 * B,), 501.0, device=dev)
+    unet.forward_nhwc(x_dev, t_probe, repeat=2)
+    torch.cuda.synchronize()
+    ops.GEMM_TC_PROFILE = None
+    flops = sum(f for f, _, _ in prof)
+    gemm_ms = sum(s.elapsed_time(e) for _, s, e in prof)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    peak_kind = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md, sustained)"
+    achieved = flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
+    fwd_flops = FLOP_PER_SAMPLE_FWD_SD2_64 * (h / 64.0) ** 2  # conv/linear scale ~ pixels; attention differs slightly
+    step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    cpu = None
+    if not a.no_cpu_baseline and world == 1:
+        times, cores = cpu_sample_seconds(a, 1)
+        cpu = {"value": 1.0 / (S * times[0]), "unit": "images/s", "cores": cores, "kind": "port",
+               "sample": "one CFG UNet evaluation (batch 2, %dx%d latent) + DDIM update for 1 image = 1 of %d steps, "
+                         "extrapolated x%d; oracle (torch fp32 restatement), MindSpore not installable" % (h, h, S, S)}
+
+    line = {
+        "metric": "images/sec @512^2 50-step DDIM CFG7.5", "value": value, "unit": "images/s", "n_gpus": world,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(a), "global_batch": B * world, "sampler": "DDIM", "sampler_steps": S,
+                   "cfg_scale": a.scale, "parallelism": "dp%d (independent prompt batches, no collective)" % world,
+                   "l2": "inputs larger than L2 (weights 1.7 GB + activations >> 126 MB)",
+                   "cuda_graph": not a.no_graph},
+        "clocks": clk,
+        "e2e": {"value": e2e, "unit": "images/s",
+                "h2d_bytes_per_step": (x_host.numel() + c_host.numel() + uc_host.numel()) * 4,
+                "d2h_bytes_per_step": out_host.numel() * 4},
+        "gpu_launches": int(launches),
+        "unet_eval_ms": ms / a.steps / S,
+        "unet_tflops_per_gpu": step_tflops,
+        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (mdx_gemm_tc: conv3x3 / 1x1 / dense)",
+                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                     "peak_kind": peak_kind, "traffic": None, "launches": len(prof), "kernel_ms_per_unet_eval": gemm_ms,
+                     "whole_step_frac": (step_tflops / peak) if step_tflops else None},
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -47,7 +47,7 @@ int64_t mdx_launch_count(void);
  *  epilogue, in this order: + bias[n] (fp32, optional) ; + rowbias[img(p) * ld_rowbias + n] (fp32, optional)
  *     ; geglu (optional): N is 2*I laid out per BLOCK_N tile as [value half | gate half] (see pack_geglu in
  *     minddiffusion_b200/weights.py), out[p, j] = value * gelu_tanh(gate), out has I columns
- *     ; + residual[p * ldr + n] (bf16, optional) ; store bf16 (out_dtype MDX_BF16) or fp32 (MDX_F32).
+ *     ; + residual[p * ldr + n] (bf16 or fp32, optional) ; store bf16 (out_dtype MDX_BF16) or fp32 (MDX_F32).
  *  block_n: 0 = choose automatically; otherwise one of 64, 128, 160, 256 (geglu packing must match).
  * --------------------------------------------------------------------------------------------------------- */
 typedef struct mdx_gemm_args {
@@ -67,6 +67,7 @@ typedef struct mdx_gemm_args {
   int64_t ld_rowbias;
   const void* residual;
   int64_t ldr;
+  int32_t residual_dtype; /* MDX_BF16 or MDX_F32 (the fp32 residual trunk, see DESIGN.md "precision") */
   int32_t geglu;
   int32_t block_n;
 } mdx_gemm_args;
@@ -108,18 +109,22 @@ int mdx_conv_direct(const mdx_conv_args* args, void* stream);
  * (the skip concat ops.Concat(axis=1) of openaimodel.py:566-571 is never materialised separately).
  * Replaces GroupNorm32(32, C) fp32 + nn.SiLU (util.py:87-108; openaimodel.py:134-137,162-163,521-523) and
  * Normalize (attention.py:83-84).  Statistics are biased (1/N) variance, accumulated in fp64.
- *  x1: [n, HW, C1] (ld1), x2: [n, HW, C2] (ld2) or NULL with C2 = 0.  gamma/beta: fp32 [C1+C2].
- *  out: [n, HW, C1+C2] with pixel stride ldo.  dtype applies to x1, x2 and out.
+ *  x1: [n, HW, C1] (ld1), x2: [n, HW, C2] (ld2) or NULL with C2 = 0 (both in_dtype).  gamma/beta: fp32 [C1+C2].
+ *  out: [n, HW, C1+C2] with pixel stride ldo (out_dtype).  Supported dtype pairs: fp32->fp32 (check mode),
+ *     bf16->bf16, fp32->bf16 (fp32 residual trunk normalised into a bf16 GEMM operand).
+ *  raw_copy: optional [n, HW, C1+C2] (ldraw, out_dtype): the un-normalised concat(x1, x2), written in the same
+ *     pass — the bf16 operand of the ResBlock's 1x1 skip_connection (openaimodel.py:167-174).  NULL to skip.
  *  stats_scratch: caller-provided, >= n*groups*2 doubles; overwritten.
  * --------------------------------------------------------------------------------------------------------- */
 int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2, int32_t n,
                   int32_t HW, int32_t groups, float eps, const float* gamma, const float* beta, int32_t silu,
-                  void* out, int64_t ldo, int32_t dtype, double* stats_scratch, void* stream);
+                  void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
+                  double* stats_scratch, void* stream);
 
 /* LayerNorm over the last dim of [rows, C] (ldx/ldo row strides). Replaces nn.LayerNorm([dim], epsilon=1e-5)
- * (attention.py:176-178).  Biased variance, fp32 statistics, one warp per row. */
+ * (attention.py:176-178).  Biased variance, fp32 statistics, one warp per row.  dtype pairs as mdx_groupnorm. */
 int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,
-                  const float* beta, void* out, int64_t ldo, int32_t dtype, void* stream);
+                  const float* beta, void* out, int64_t ldo, int32_t in_dtype, int32_t out_dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Multi-head attention  o = softmax(q k^T * scale) v  without materialising q k^T
@@ -144,7 +149,7 @@ int mdx_timestep_embedding(const float* t, int32_t n, int32_t dim, float max_per
  *  mdx_nchw_to_nhwc: x fp32 NCHW [n, C, H, W] -> out [n*repeat, H, W, C] (dtype), batch index taken mod n:
  *     the CFG ops.concat((x, x)) of plms.py:192 without a copy of its own.
  *  mdx_nhwc_to_nchw: x [n, H, W, C] (dtype) -> fp32 NCHW.
- *  mdx_upsample_nearest2x: ops.ResizeNearestNeighbor (openaimodel.py:53-60) on NHWC.
+ *  mdx_upsample_nearest2x: ops.ResizeNearestNeighbor (openaimodel.py:53-60) on NHWC (fp32->bf16 converts).
  *  mdx_concat_channels: ops.Concat(axis=1) (openaimodel.py:567) on NHWC rows.
  *  mdx_im2col3x3: gathers 3x3 patches (stride, pad 1) into [n*OH*OW, 9*C] rows, K order (r,s,c) — feeds the
  *     stride-2 Downsample conv (openaimodel.py:80-88) to mdx_gemm_tc.
@@ -159,12 +164,12 @@ int mdx_nhwc_to_nchw(const void* x, int32_t n, int32_t C, int32_t H, int32_t W, 
 /* same, reading the first C channels of rows with pixel stride ldx >= C */
 int mdx_nhwc_to_nchw_ld(const void* x, int64_t ldx, int32_t n, int32_t C, int32_t H, int32_t W, int32_t dtype,
                         float* out, void* stream);
-int mdx_upsample_nearest2x(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, void* out, int32_t dtype,
-                           void* stream);
+int mdx_upsample_nearest2x(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, void* out, int32_t in_dtype,
+                           int32_t out_dtype, void* stream);
 int mdx_concat_channels(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
                         int64_t rows, void* out, int64_t ldo, int32_t dtype, void* stream);
 int mdx_im2col3x3(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, int32_t stride, void* out,
-                  int32_t dtype, void* stream);
+                  int32_t in_dtype, int32_t out_dtype, void* stream);
 int mdx_cast(const void* x, int32_t in_dtype, void* out, int32_t out_dtype, int64_t count, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------

@@ -36,6 +36,7 @@ class GemmArgs(ctypes.Structure):
         ("ld_rowbias", c_i64),
         ("residual", c_p),
         ("ldr", c_i64),
+        ("residual_dtype", c_int),
         ("geglu", c_int),
         ("block_n", c_int),
     ]
@@ -63,8 +64,8 @@ SIGNATURES = {
     "mdx_gemm_tc_pick_block_n": (c_int, [c_int, c_int]),
     "mdx_conv_direct": (c_int, [ctypes.POINTER(ConvArgs), c_p]),
     "mdx_groupnorm": (c_int, [c_p, c_i64, c_int, c_p, c_i64, c_int, c_int, c_int, c_int, c_f, c_p, c_p, c_int, c_p,
-                              c_i64, c_int, c_p, c_p]),
-    "mdx_layernorm": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_p, c_p, c_p, c_i64, c_int, c_p]),
+                              c_i64, c_p, c_i64, c_int, c_int, c_p, c_p]),
+    "mdx_layernorm": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_p, c_p, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_attention": (c_int, [c_p, c_i64, c_p, c_i64, c_p, c_i64, c_p, c_i64, c_int, c_int, c_int, c_int, c_int, c_f,
                               c_int, c_p]),
     "mdx_geglu": (c_int, [c_p, c_i64, c_int, c_int, c_p, c_i64, c_int, c_p]),
@@ -73,9 +74,9 @@ SIGNATURES = {
     "mdx_nchw_to_nhwc_pad": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_int, c_p]),
     "mdx_nhwc_to_nchw": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_p, c_p]),
     "mdx_nhwc_to_nchw_ld": (c_int, [c_p, c_i64, c_int, c_int, c_int, c_int, c_int, c_p, c_p]),
-    "mdx_upsample_nearest2x": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p, c_int, c_p]),
+    "mdx_upsample_nearest2x": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p, c_int, c_int, c_p]),
     "mdx_concat_channels": (c_int, [c_p, c_i64, c_int, c_p, c_i64, c_int, c_i64, c_p, c_i64, c_int, c_p]),
-    "mdx_im2col3x3": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_p, c_int, c_p]),
+    "mdx_im2col3x3": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_p, c_int, c_int, c_p]),
     "mdx_cast": (c_int, [c_p, c_int, c_p, c_int, c_i64, c_p]),
     "mdx_sampler_plms_step": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p,
                                       c_int, c_int, c_int, c_int, c_p]),

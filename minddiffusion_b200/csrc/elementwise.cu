@@ -61,14 +61,30 @@ __global__ void nhwc_to_nchw_kernel(const T* __restrict__ x, int n, int C, int H
   }
 }
 
-// 16-byte vector copies: V elements per vector
-template <typename T>
-__global__ void upsample2x_kernel(const T* __restrict__ x, int n, int H, int W, int C, T* __restrict__ out) {
-  constexpr int V = 16 / sizeof(T);
-  const int CV = C / V;
+// 4 channels per thread; TI -> TO conversion on the fly (fp32 trunk -> bf16 conv operand)
+template <typename T> __device__ __forceinline__ void ld4(const T* p, float (&v)[4]);
+template <> __device__ __forceinline__ void ld4<float>(const float* p, float (&v)[4]) {
+  float4 a = *reinterpret_cast<const float4*>(p);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+template <> __device__ __forceinline__ void ld4<bf16>(const bf16* p, float (&v)[4]) {
+  uint2 u = *reinterpret_cast<const uint2*>(p);
+  float2 f = unpack_bf16x2(u.x); v[0] = f.x; v[1] = f.y;
+  f = unpack_bf16x2(u.y); v[2] = f.x; v[3] = f.y;
+}
+template <typename T> __device__ __forceinline__ void st4(T* p, const float (&v)[4]);
+template <> __device__ __forceinline__ void st4<float>(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+template <> __device__ __forceinline__ void st4<bf16>(bf16* p, const float (&v)[4]) {
+  uint2 u; u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+template <typename TI, typename TO>
+__global__ void upsample2x_kernel(const TI* __restrict__ x, int n, int H, int W, int C, TO* __restrict__ out) {
+  const int CV = C / 4;
   const long long total = (long long)n * 2 * H * 2 * W * CV;
-  const uint4* src = reinterpret_cast<const uint4*>(x);
-  uint4* dst = reinterpret_cast<uint4*>(out);
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int cv = (int)(i % CV);
     long long pix = i / CV;
@@ -76,7 +92,9 @@ __global__ void upsample2x_kernel(const T* __restrict__ x, int n, int H, int W, 
     pix /= 2 * W;
     const int oy = (int)(pix % (2 * H));
     const int b = (int)(pix / (2 * H));
-    dst[i] = src[(((long long)b * H + (oy >> 1)) * W + (ox >> 1)) * CV + cv];
+    float v[4];
+    ld4<TI>(x + ((((long long)b * H + (oy >> 1)) * W + (ox >> 1)) * CV + cv) * 4, v);
+    st4<TO>(out + i * 4, v);
   }
 }
 
@@ -95,13 +113,11 @@ __global__ void concat_kernel(const T* __restrict__ x1, long long ld1, int C1, c
   }
 }
 
-template <typename T>
-__global__ void im2col3x3_kernel(const T* __restrict__ x, int n, int H, int W, int C, int stride, int OH, int OW,
-                                 T* __restrict__ out) {
-  constexpr int V = 16 / sizeof(T);
-  const int CV = C / V;
+template <typename TI, typename TO>
+__global__ void im2col3x3_kernel(const TI* __restrict__ x, int n, int H, int W, int C, int stride, int OH, int OW,
+                                 TO* __restrict__ out) {
+  const int CV = C / 4;
   const long long total = (long long)n * OH * OW * 9 * CV;
-  uint4* dst = reinterpret_cast<uint4*>(out);
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int cv = (int)(i % CV);
     long long r = i / CV;
@@ -112,10 +128,9 @@ __global__ void im2col3x3_kernel(const T* __restrict__ x, int n, int H, int W, i
     const int oy = (int)(r % OH);
     const int b = (int)(r / OH);
     const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (iy >= 0 && iy < H && ix >= 0 && ix < W)
-      v = *reinterpret_cast<const uint4*>(x + (((long long)b * H + iy) * W + ix) * C + cv * V);
-    dst[i] = v;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (iy >= 0 && iy < H && ix >= 0 && ix < W) ld4<TI>(x + (((long long)b * H + iy) * W + ix) * C + cv * 4, v);
+    st4<TO>(out + i * 4, v);
   }
 }
 
@@ -196,17 +211,22 @@ extern "C" int mdx_nhwc_to_nchw(const void* x, int32_t n, int32_t C, int32_t H, 
 }
 
 extern "C" int mdx_upsample_nearest2x(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, void* out,
-                                      int32_t dtype, void* stream) {
+                                      int32_t in_dtype, int32_t out_dtype, void* stream) {
   MDX_CHECK_ARG(x && out && n > 0 && H > 0 && W > 0 && C > 0, "mdx_upsample_nearest2x: bad arguments");
-  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_upsample_nearest2x: bad dtype");
-  const int V = dtype == MDX_BF16 ? 8 : 4;
-  MDX_CHECK_ARG(C % V == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0, "mdx_upsample_nearest2x: alignment");
+  MDX_CHECK_ARG(C % 4 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0, "mdx_upsample_nearest2x: alignment");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const long long total = (long long)n * 4 * H * W * (C / V);
-  if (dtype == MDX_BF16)
-    upsample2x_kernel<bf16><<<blocks_for(total, 256), 256, 0, st>>>((const bf16*)x, n, H, W, C, (bf16*)out);
-  else
-    upsample2x_kernel<float><<<blocks_for(total, 256), 256, 0, st>>>((const float*)x, n, H, W, C, (float*)out);
+  const long long total = (long long)n * 4 * H * W * (C / 4);
+  const unsigned g = blocks_for(total, 256);
+  if (in_dtype == MDX_BF16 && out_dtype == MDX_BF16)
+    upsample2x_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, n, H, W, C, (bf16*)out);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_BF16)
+    upsample2x_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, (bf16*)out);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_F32)
+    upsample2x_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, (float*)out);
+  else {
+    mdx_set_error("mdx_upsample_nearest2x: unsupported dtypes %d -> %d", in_dtype, out_dtype);
+    return MDX_ERR_INVALID;
+  }
   LAUNCHED(1);
 }
 
@@ -226,18 +246,23 @@ extern "C" int mdx_concat_channels(const void* x1, int64_t ld1, int32_t C1, cons
 }
 
 extern "C" int mdx_im2col3x3(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, int32_t stride, void* out,
-                             int32_t dtype, void* stream) {
+                             int32_t in_dtype, int32_t out_dtype, void* stream) {
   MDX_CHECK_ARG(x && out && n > 0 && H > 0 && W > 0 && C > 0 && stride > 0, "mdx_im2col3x3: bad arguments");
-  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_im2col3x3: bad dtype");
-  const int V = dtype == MDX_BF16 ? 8 : 4;
-  MDX_CHECK_ARG(C % V == 0, "mdx_im2col3x3: C must be a multiple of %d", V);
+  MDX_CHECK_ARG(C % 4 == 0, "mdx_im2col3x3: C must be a multiple of 4");
   const int OH = (H + 2 - 3) / stride + 1, OW = (W + 2 - 3) / stride + 1;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const long long total = (long long)n * OH * OW * 9 * (C / V);
-  if (dtype == MDX_BF16)
-    im2col3x3_kernel<bf16><<<blocks_for(total, 256), 256, 0, st>>>((const bf16*)x, n, H, W, C, stride, OH, OW, (bf16*)out);
-  else
-    im2col3x3_kernel<float><<<blocks_for(total, 256), 256, 0, st>>>((const float*)x, n, H, W, C, stride, OH, OW, (float*)out);
+  const long long total = (long long)n * OH * OW * 9 * (C / 4);
+  const unsigned g = blocks_for(total, 256);
+  if (in_dtype == MDX_BF16 && out_dtype == MDX_BF16)
+    im2col3x3_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, n, H, W, C, stride, OH, OW, (bf16*)out);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_BF16)
+    im2col3x3_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, stride, OH, OW, (bf16*)out);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_F32)
+    im2col3x3_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, stride, OH, OW, (float*)out);
+  else {
+    mdx_set_error("mdx_im2col3x3: unsupported dtypes %d -> %d", in_dtype, out_dtype);
+    return MDX_ERR_INVALID;
+  }
   LAUNCHED(1);
 }
 

@@ -38,8 +38,9 @@ struct TcParams {
   const float* bias;
   const float* rowbias;
   long long ld_rowbias;
-  const bf16* residual;
+  const void* residual;
   long long ldr;
+  int res_f32;
   int geglu;
 };
 
@@ -215,8 +216,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
               }
             }
-            if (p.residual) {
-              const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.ldr + col0);
+            if (p.residual && p.res_f32) {
+              const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + pix * p.ldr + col0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                float4 b = __ldg(rp + i);
+                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+              }
+            } else if (p.residual) {
+              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ldr + col0);
 #pragma unroll
               for (int i = 0; i < 2; ++i) {
                 uint4 u = __ldg(rp + i);
@@ -448,8 +456,9 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->out) & 15) == 0 && a->ldc % 8 == 0,
                 "mdx_gemm_tc: out must be 16-byte aligned with ldc %% 8 == 0");
   if (a->residual)
-    MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->residual) & 15) == 0 && a->ldr % 8 == 0,
-                  "mdx_gemm_tc: residual must be 16-byte aligned with ldr %% 8 == 0");
+    MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->residual) & 15) == 0 && a->ldr % 8 == 0 &&
+                      (a->residual_dtype == MDX_BF16 || a->residual_dtype == MDX_F32),
+                  "mdx_gemm_tc: residual must be 16-byte aligned with ldr %% 8 == 0, dtype bf16 or fp32");
   if (a->bias) MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->bias) & 15) == 0, "mdx_gemm_tc: bias alignment");
   if (a->rowbias)
     MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->rowbias) & 15) == 0 && a->ld_rowbias % 4 == 0,
@@ -488,7 +497,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   p.num_tiles = (int)nt;
   p.out = a->out; p.ldc = a->ldc; p.out_f32 = a->out_dtype == MDX_F32;
   p.bias = a->bias; p.rowbias = a->rowbias; p.ld_rowbias = a->ld_rowbias;
-  p.residual = reinterpret_cast<const bf16*>(a->residual); p.ldr = a->ldr;
+  p.residual = a->residual; p.ldr = a->ldr; p.res_f32 = a->residual_dtype == MDX_F32;
   p.geglu = a->geglu;
 
   CUtensorMap maps[3];

@@ -14,15 +14,18 @@ extern std::atomic<long long> g_mdx_launches;
 
 namespace {
 
+// 8 consecutive channels per thread, whatever the storage type (fp32: two 16-byte accesses, bf16: one)
 template <typename T> struct Vec;
 template <> struct Vec<float> {
-  static constexpr int N = 4;
-  __device__ static void load(const float* p, float (&v)[4]) {
-    float4 u = *reinterpret_cast<const float4*>(p);
-    v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
+  static constexpr int N = 8;
+  __device__ static void load(const float* p, float (&v)[8]) {
+    float4 a = *reinterpret_cast<const float4*>(p);
+    float4 b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
   }
-  __device__ static void store(float* p, const float (&v)[4]) {
+  __device__ static void store(float* p, const float (&v)[8]) {
     *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
   }
 };
 template <> struct Vec<bf16> {
@@ -52,6 +55,7 @@ struct GnP {
   const float* gamma; const float* beta;
   int silu;
   void* out; long long ldo;
+  void* raw; long long ldraw;  // optional un-normalised copy of concat(x1, x2) in the out dtype
   double* stats;
 };
 
@@ -59,9 +63,9 @@ struct GnP {
 template <typename T>
 __global__ void gn_stats_kernel(const GnP p) {
   constexpr int V = Vec<T>::N;
-  __shared__ float bins[64][2];
+  __shared__ double bins[64][2];  // fp64 so that the (unordered) atomics cannot change the rounded result
   const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y) (&bins[0][0])[i] = 0.f;
+  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y) (&bins[0][0])[i] = 0.0;
   __syncthreads();
   const int C = p.C1 + p.C2;
   const int c0 = threadIdx.x * V;
@@ -87,16 +91,16 @@ __global__ void gn_stats_kernel(const GnP p) {
 #pragma unroll
     for (int i = 0; i < V; ++i) {
       const int g = (c0 + i) / p.cpg;
-      atomicAdd(&bins[g][0], s[i]);
-      atomicAdd(&bins[g][1], ss[i]);
+      atomicAdd(&bins[g][0], (double)s[i]);
+      atomicAdd(&bins[g][1], (double)ss[i]);
     }
   }
   __syncthreads();
   for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y)
-    atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (double)(&bins[0][0])[i]);
+    atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (&bins[0][0])[i]);
 }
 
-template <typename T>
+template <typename T, typename TO>
 __global__ void gn_apply_kernel(const GnP p) {
   constexpr int V = Vec<T>::N;
   const int C = p.C1 + p.C2;
@@ -126,24 +130,26 @@ __global__ void gn_apply_kernel(const GnP p) {
   const int r0 = blockIdx.x * p.rows_per_block;
   const int r1 = min(p.HW, r0 + p.rows_per_block);
   const T* base = src + (long long)img * p.HW * ld + cc;
-  T* obase = reinterpret_cast<T*>(p.out) + (long long)img * p.HW * p.ldo + c0;
+  TO* obase = reinterpret_cast<TO*>(p.out) + (long long)img * p.HW * p.ldo + c0;
+  TO* rbase = p.raw ? reinterpret_cast<TO*>(p.raw) + (long long)img * p.HW * p.ldraw + c0 : nullptr;
   for (int r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
     float v[V];
     Vec<T>::load(base + (long long)r * ld, v);
+    if (rbase) Vec<TO>::store(rbase + (long long)r * p.ldraw, v);
 #pragma unroll
     for (int i = 0; i < V; ++i) {
       float y = fmaf(v[i], a[i], b[i]);
       v[i] = p.silu ? silu_f(y) : y;
     }
-    Vec<T>::store(obase + (long long)r * p.ldo, v);
+    Vec<TO>::store(obase + (long long)r * p.ldo, v);
   }
 }
 
 // ---------------- LayerNorm: one warp per row, values held in registers ----------------
-template <typename T, int MAXV>
+template <typename T, typename TO, int MAXV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, long long ldx, int rows, int C,
                                                         float eps, const float* __restrict__ gamma,
-                                                        const float* __restrict__ beta, T* __restrict__ out,
+                                                        const float* __restrict__ beta, TO* __restrict__ out,
                                                         long long ldo) {
   constexpr int V = Vec<T>::N;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -175,7 +181,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x,
   }
   q = warp_sum(q);
   const float rstd = rsqrtf(q / (float)C + eps);
-  T* orow = out + (long long)warp * ldo;
+  TO* orow = out + (long long)warp * ldo;
 #pragma unroll
   for (int j = 0; j < MAXV; ++j) {
     const int vi = lane + j * 32;
@@ -186,12 +192,12 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x,
         const int c = vi * V + i;
         y[i] = (v[j][i] - mean) * rstd * gamma[c] + beta[c];
       }
-      Vec<T>::store(orow + vi * V, y);
+      Vec<TO>::store(orow + vi * V, y);
     }
   }
 }
 
-template <typename T>
+template <typename T, typename TO>
 int launch_gn(GnP p, cudaStream_t st) {
   constexpr int V = Vec<T>::N;
   const int C = p.C1 + p.C2;
@@ -212,7 +218,7 @@ int launch_gn(GnP p, cudaStream_t st) {
   MDX_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, sizeof(double) * 2 * p.groups * p.n, st));
   gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
   MDX_CHECK_LAUNCH();
-  gn_apply_kernel<T><<<grid, block, 0, st>>>(p);
+  gn_apply_kernel<T, TO><<<grid, block, 0, st>>>(p);
   MDX_CHECK_LAUNCH();
   g_mdx_launches.fetch_add(2, std::memory_order_relaxed);
   return MDX_OK;
@@ -222,44 +228,53 @@ int launch_gn(GnP p, cudaStream_t st) {
 
 extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
                              int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma,
-                             const float* beta, int32_t silu, void* out, int64_t ldo, int32_t dtype,
-                             double* stats_scratch, void* stream) {
+                             const float* beta, int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw,
+                             int32_t in_dtype, int32_t out_dtype, double* stats_scratch, void* stream) {
   MDX_CHECK_ARG(x1 && out && gamma && beta && stats_scratch, "mdx_groupnorm: NULL operand");
   MDX_CHECK_ARG(n > 0 && HW > 0 && C1 > 0 && C2 >= 0, "mdx_groupnorm: empty problem");
   MDX_CHECK_ARG(C2 == 0 || x2 != nullptr, "mdx_groupnorm: x2 is NULL but C2 > 0");
   const int C = C1 + C2;
   MDX_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "mdx_groupnorm: C=%d not divisible by groups=%d", C,
                 groups);
-  const int V = dtype == MDX_BF16 ? 8 : 4;
-  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_groupnorm: bad dtype");
-  MDX_CHECK_ARG(C1 % V == 0 && C2 % V == 0 && ld1 % V == 0 && ld2 % V == 0 && ldo % V == 0,
-                "mdx_groupnorm: channels and row strides must be multiples of %d", V);
-  MDX_CHECK_ARG(((uintptr_t)x1 & 15) == 0 && ((uintptr_t)x2 & 15) == 0 && ((uintptr_t)out & 15) == 0,
+  MDX_CHECK_ARG((in_dtype == MDX_BF16 || in_dtype == MDX_F32) && (out_dtype == MDX_BF16 || out_dtype == MDX_F32),
+                "mdx_groupnorm: bad dtype");
+  MDX_CHECK_ARG(!(in_dtype == MDX_BF16 && out_dtype == MDX_F32), "mdx_groupnorm: bf16 -> fp32 is not supported");
+  MDX_CHECK_ARG(C1 % 8 == 0 && C2 % 8 == 0 && ld1 % 8 == 0 && ld2 % 8 == 0 && ldo % 8 == 0 && ldraw % 8 == 0,
+                "mdx_groupnorm: channels and row strides must be multiples of 8");
+  MDX_CHECK_ARG(((uintptr_t)x1 & 15) == 0 && ((uintptr_t)x2 & 15) == 0 && ((uintptr_t)out & 15) == 0 &&
+                    ((uintptr_t)raw_copy & 15) == 0,
                 "mdx_groupnorm: operands must be 16-byte aligned");
   GnP p;
   p.x1 = x1; p.ld1 = ld1; p.C1 = C1; p.x2 = x2; p.ld2 = ld2; p.C2 = C2;
   p.n = n; p.HW = HW; p.groups = groups; p.cpg = C / groups; p.rows_per_block = 0;
-  p.eps = eps; p.gamma = gamma; p.beta = beta; p.silu = silu; p.out = out; p.ldo = ldo; p.stats = stats_scratch;
+  p.eps = eps; p.gamma = gamma; p.beta = beta; p.silu = silu; p.out = out; p.ldo = ldo;
+  p.raw = raw_copy; p.ldraw = ldraw; p.stats = stats_scratch;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  return dtype == MDX_BF16 ? launch_gn<bf16>(p, st) : launch_gn<float>(p, st);
+  if (in_dtype == MDX_BF16) return launch_gn<bf16, bf16>(p, st);
+  if (out_dtype == MDX_BF16) return launch_gn<float, bf16>(p, st);
+  return launch_gn<float, float>(p, st);
 }
 
 extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,
-                             const float* beta, void* out, int64_t ldo, int32_t dtype, void* stream) {
+                             const float* beta, void* out, int64_t ldo, int32_t in_dtype, int32_t out_dtype,
+                             void* stream) {
   MDX_CHECK_ARG(x && out && gamma && beta, "mdx_layernorm: NULL operand");
   MDX_CHECK_ARG(rows > 0 && C > 0, "mdx_layernorm: empty problem");
-  MDX_CHECK_ARG(dtype == MDX_BF16 || dtype == MDX_F32, "mdx_layernorm: bad dtype");
-  const int V = dtype == MDX_BF16 ? 8 : 4;
-  MDX_CHECK_ARG(C % V == 0 && ldx % V == 0 && ldo % V == 0, "mdx_layernorm: C and strides must be multiples of %d", V);
+  MDX_CHECK_ARG((in_dtype == MDX_BF16 || in_dtype == MDX_F32) && (out_dtype == MDX_BF16 || out_dtype == MDX_F32),
+                "mdx_layernorm: bad dtype");
+  MDX_CHECK_ARG(!(in_dtype == MDX_BF16 && out_dtype == MDX_F32), "mdx_layernorm: bf16 -> fp32 is not supported");
+  MDX_CHECK_ARG(C % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0, "mdx_layernorm: C and strides must be multiples of 8");
   MDX_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0, "mdx_layernorm: 16-byte alignment");
-  MDX_CHECK_ARG(C / V <= 12 * 32, "mdx_layernorm: C=%d too large", C);
+  MDX_CHECK_ARG(C / 8 <= 8 * 32, "mdx_layernorm: C=%d too large (max 2048)", C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int wpb = 8;
   dim3 grid((rows + wpb - 1) / wpb), block(wpb * 32);
-  if (dtype == MDX_BF16)
-    layernorm_kernel<bf16, 12><<<grid, block, 0, st>>>((const bf16*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
+  if (in_dtype == MDX_BF16)
+    layernorm_kernel<bf16, bf16, 8><<<grid, block, 0, st>>>((const bf16*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
+  else if (out_dtype == MDX_BF16)
+    layernorm_kernel<float, bf16, 8><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
   else
-    layernorm_kernel<float, 12><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (float*)out, ldo);
+    layernorm_kernel<float, float, 8><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (float*)out, ldo);
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;

@@ -12,6 +12,8 @@ from . import _lib
 from ._lib import ConvArgs, GemmArgs, check
 
 F32, BF16 = 0, 1
+# bench.py sets this to a list to time every mdx_gemm_tc launch with CUDA events: entries (flops, start, end)
+GEMM_TC_PROFILE = None
 _DT = {torch.float32: F32, torch.bfloat16: BF16}
 
 
@@ -108,15 +110,21 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
         args.rowbias = rowbias.data_ptr()
         args.ld_rowbias = rowbias.stride(0)
     if residual is not None:
-        if residual.dtype != torch.bfloat16:
-            raise TypeError("residual must be bfloat16")
         rr, rc, ldr = _rows_ld(residual)
         if rr != M or rc != n_out:
             raise ValueError("residual shape mismatch")
         args.residual = residual.data_ptr()
         args.ldr = ldr
+        args.residual_dtype = _dt(residual)
     args.geglu = 1 if geglu else 0
     args.block_n = block_n
+    if GEMM_TC_PROFILE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
+        e1.record()
+        GEMM_TC_PROFILE.append((2.0 * M * N * ktot, e0, e1))
+        return out
     check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
     return out
 
@@ -163,8 +171,11 @@ def conv_direct(x, w, kh=1, kw=1, stride=1, pad=0, upsample=False, pre_silu=Fals
     return out
 
 
-def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=None, scratch=None):
-    """GroupNorm(+SiLU) over NHWC ``[n, H, W, C]`` (optionally over concat(x1, x2) along C)."""
+def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=None, scratch=None, out_dtype=None,
+              raw_copy=False):
+    """GroupNorm(+SiLU) over NHWC ``[n, H, W, C]`` (optionally over concat(x1, x2) along C).
+    out_dtype: dtype of the result (default: dtype of x1).  raw_copy=True also returns the un-normalised
+    concat(x1, x2) converted to out_dtype (second return value)."""
     lib = _lib.load()
     n = x1.shape[0]
     rows, C1, ld1 = _rows_ld(x1)
@@ -174,29 +185,31 @@ def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=Non
         r2, C2, ld2 = _rows_ld(x2)
         if r2 != rows or x2.dtype != x1.dtype:
             raise ValueError("x2 must match x1 in rows and dtype")
+    odt = out_dtype or x1.dtype
     if out is None:
-        out = torch.empty(tuple(x1.shape[:-1]) + (C1 + C2,), dtype=x1.dtype, device=x1.device)
+        out = torch.empty(tuple(x1.shape[:-1]) + (C1 + C2,), dtype=odt, device=x1.device)
     _, oc, ldo = _rows_ld(out)
     if oc != C1 + C2:
         raise ValueError("out channel mismatch")
+    raw = torch.empty_like(out) if raw_copy else None
     if scratch is None:
         scratch = torch.empty(n * groups * 2, dtype=torch.float64, device=x1.device)
     elif scratch.dtype != torch.float64 or scratch.numel() < n * groups * 2:
         raise ValueError("scratch must hold n*groups*2 float64")
     check(lib.mdx_groupnorm(_p(x1), ld1, C1, _p(x2), ld2, C2, n, HW, groups, float(eps), _p(_f32(gamma, "gamma")),
-                            _p(_f32(beta, "beta")), int(silu), _p(out), ldo, _dt(x1), _p(scratch), _stream()),
-          "mdx_groupnorm")
-    return out
+                            _p(_f32(beta, "beta")), int(silu), _p(out), ldo, _p(raw), C1 + C2 if raw_copy else 0,
+                            _dt(x1), _dt(out), _p(scratch), _stream()), "mdx_groupnorm")
+    return (out, raw) if raw_copy else out
 
 
-def layernorm(x, gamma, beta, eps=1e-5, out=None):
+def layernorm(x, gamma, beta, eps=1e-5, out=None, out_dtype=None):
     lib = _lib.load()
     rows, C, ldx = _rows_ld(x)
     if out is None:
-        out = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+        out = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
     _, _, ldo = _rows_ld(out)
     check(lib.mdx_layernorm(_p(x), ldx, rows, C, float(eps), _p(_f32(gamma, "gamma")), _p(_f32(beta, "beta")),
-                            _p(out), ldo, _dt(x), _stream()), "mdx_layernorm")
+                            _p(out), ldo, _dt(x), _dt(out), _stream()), "mdx_layernorm")
     return out
 
 
@@ -258,13 +271,14 @@ def nhwc_to_nchw(x, C=None):
     return out
 
 
-def upsample_nearest2x(x):
+def upsample_nearest2x(x, out_dtype=None):
     lib = _lib.load()
     n, H, W, C = x.shape
     if not x.is_contiguous():
         raise ValueError("x must be contiguous")
-    out = torch.empty((n, 2 * H, 2 * W, C), dtype=x.dtype, device=x.device)
-    check(lib.mdx_upsample_nearest2x(_p(x), n, H, W, C, _p(out), _dt(x), _stream()), "mdx_upsample_nearest2x")
+    out = torch.empty((n, 2 * H, 2 * W, C), dtype=out_dtype or x.dtype, device=x.device)
+    check(lib.mdx_upsample_nearest2x(_p(x), n, H, W, C, _p(out), _dt(x), _dt(out), _stream()),
+          "mdx_upsample_nearest2x")
     return out
 
 
@@ -280,14 +294,14 @@ def concat_channels(x1, x2):
     return out
 
 
-def im2col3x3(x, stride):
+def im2col3x3(x, stride, out_dtype=None):
     lib = _lib.load()
     n, H, W, C = x.shape
     if not x.is_contiguous():
         raise ValueError("x must be contiguous")
     OH, OW = (H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1
-    out = torch.empty((n, OH, OW, 9 * C), dtype=x.dtype, device=x.device)
-    check(lib.mdx_im2col3x3(_p(x), n, H, W, C, stride, _p(out), _dt(x), _stream()), "mdx_im2col3x3")
+    out = torch.empty((n, OH, OW, 9 * C), dtype=out_dtype or x.dtype, device=x.device)
+    check(lib.mdx_im2col3x3(_p(x), n, H, W, C, stride, _p(out), _dt(x), _dt(out), _stream()), "mdx_im2col3x3")
     return out
 
 

@@ -21,7 +21,7 @@ graph on CUDA-core fp32 kernels, used to separate orchestration errors from bf16
 import numpy as np
 import torch
 
-from . import ops
+from . import _lib, ops
 
 PREFIX = "model.diffusion_model."
 
@@ -115,6 +115,7 @@ class UNetModel:
         self._ctx = None
         self._graphs = {}
         self.use_cuda_graph = False
+        self.replayed_launches = 0  # kernels launched by graph replays (they bypass the C ABI's own counter)
         self._pack(params)
 
     # ------------------------------------------------------------------------------------------------
@@ -223,17 +224,19 @@ class UNetModel:
     # ------------------------------------------------------------------------------------------------
     # op helpers (bf16 tensor-core path / fp32 check path)
     # ------------------------------------------------------------------------------------------------
-    def _conv3(self, x, w, b, rowbias=None, residual=None, skips=None):
-        """3x3 stride-1 conv on NHWC x; `skips`: raw tensors whose fused 1x1 conv is K-concatenated (bf16)."""
+    def _conv3(self, x, w, b, rowbias=None, residual=None, skips=None, trunk=False):
+        """3x3 stride-1 conv on NHWC x; `skips`: raw bf16 tensors whose fused 1x1 conv is K-concatenated (bf16
+        mode); trunk=True writes the fp32 residual stream."""
         n, H, W, _ = x.shape
         if self.bf16:
             segs = [(x, 9)] + [(s, 1) for s in (skips or [])]
-            out = ops.gemm_tc(segs, w, bias=b, rowbias=rowbias, residual=residual)
+            out = ops.gemm_tc(segs, w, bias=b, rowbias=rowbias, residual=residual,
+                              out_dtype=torch.float32 if trunk else torch.bfloat16)
             return out.view(n, H, W, -1)
         return ops.conv_direct(x, w, 3, 3, 1, 1, bias=b, rowbias=rowbias, residual=residual)
 
-    def _linear(self, x, w, b=None, residual=None, geglu_bn=None, out=None):
-        """Dense layer on rows; x: [..., K] view."""
+    def _linear(self, x, w, b=None, residual=None, geglu_bn=None, out=None, trunk=False):
+        """Dense layer on rows; x: [..., K] view. trunk=True writes the fp32 residual stream (bf16 mode)."""
         if self.bf16:
             x2 = x.reshape(-1, x.shape[-1]) if x.is_contiguous() else x
             if x2.dim() != 2:
@@ -241,29 +244,36 @@ class UNetModel:
             r2 = residual.reshape(-1, residual.shape[-1]) if residual is not None else None
             if geglu_bn:
                 return ops.gemm_tc([(x2, 1)], w, bias=b, geglu=True, block_n=geglu_bn, out=out)
-            return ops.gemm_tc([(x2, 1)], w, bias=b, residual=r2, out=out)
+            return ops.gemm_tc([(x2, 1)], w, bias=b, residual=r2, out=out,
+                               out_dtype=torch.float32 if trunk else torch.bfloat16)
         x2 = x.reshape(-1, x.shape[-1])
         r2 = residual.reshape(-1, residual.shape[-1]) if residual is not None else None
         return ops.conv_direct(x2, w, bias=b, residual=r2, out=out)
 
     # ------------------------------------------------------------------------------------------------
-    # blocks
+    # blocks.  bf16 mode keeps the residual stream ("trunk": block inputs/outputs, the skip list and the
+    # transformer's token stream) in fp32 and every GEMM operand in bf16; see DESIGN.md "precision".
     # ------------------------------------------------------------------------------------------------
     def _res(self, pre, layer, x1, x2, emb_all):
         L = self.L
         cin, cout = layer[1], layer[2]
         g1, b1 = L[pre + "n1"]
-        h = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch)
+        w2, bb2, has_skip = L[pre + "c2"]
+        raw = None
+        if self.bf16 and has_skip:  # the same pass also emits the bf16 operand of the 1x1 skip conv
+            h, raw = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch,
+                                   out_dtype=self.dtype, raw_copy=True)
+        else:
+            h = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch, out_dtype=self.dtype)
         w1, bb1 = L[pre + "c1"]
         off, _ = L[pre + "emb"]
         h = self._conv3(h, w1, bb1, rowbias=emb_all[:, off:off + cout])
         g2, b2 = L[pre + "n2"]
         h = ops.groupnorm(h, g2, b2, 32, 1e-5, silu=True, scratch=self._gn_scratch)
-        w2, bb2, has_skip = L[pre + "c2"]
         if not has_skip:
-            return self._conv3(h, w2, bb2, residual=x1)
+            return self._conv3(h, w2, bb2, residual=x1, trunk=True)
         if self.bf16:
-            return self._conv3(h, w2, bb2, skips=[x1] if x2 is None else [x1, x2])
+            return self._conv3(h, w2, bb2, skips=[raw], trunk=True)
         xin = x1 if x2 is None else ops.concat_channels(x1, x2)
         ws, bs = L[pre + "skip"]
         sk = ops.conv_direct(xin, ws, bias=bs)
@@ -275,45 +285,47 @@ class UNetModel:
         n, H, W, _ = x.shape
         N = H * W
         scale = dh ** -0.5
+        dt = self.dtype
         gn, bn_ = L[pre + "norm"]
-        hn = ops.groupnorm(x, gn, bn_, 32, 1e-6, silu=False, scratch=self._gn_scratch)
+        hn = ops.groupnorm(x, gn, bn_, 32, 1e-6, silu=False, scratch=self._gn_scratch, out_dtype=dt)
         w, b = L[pre + "proj_in"]
-        t = self._linear(hn, w, b)                       # [n*N, C]
+        t = self._linear(hn, w, b, trunk=True)           # [n*N, C] token stream
         C = t.shape[-1]
         for d in range(self.depth):
             tb = pre + "transformer_blocks.%d." % d
-            a = ops.layernorm(t, *L[tb + "norm1"], eps=1e-5)
+            a = ops.layernorm(t, *L[tb + "norm1"], eps=1e-5, out_dtype=dt)
             qkv = self._linear(a, L[tb + "qkv"]).view(n, N, 3 * C)
             o = ops.attention(qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:], heads, scale)
-            t = self._linear(o, *L[tb + "o1"], residual=t)
-            a = ops.layernorm(t, *L[tb + "norm2"], eps=1e-5)
+            t = self._linear(o, *L[tb + "o1"], residual=t, trunk=True)
+            a = ops.layernorm(t, *L[tb + "norm2"], eps=1e-5, out_dtype=dt)
             q = self._linear(a, L[tb + "q2"]).view(n, N, C)
             kv = self._ctx[tb]
             o = ops.attention(q, kv[:, :, :C], kv[:, :, C:], heads, scale)
-            t = self._linear(o, *L[tb + "o2"], residual=t)
-            a = ops.layernorm(t, *L[tb + "norm3"], eps=1e-5)
+            t = self._linear(o, *L[tb + "o2"], residual=t, trunk=True)
+            a = ops.layernorm(t, *L[tb + "norm3"], eps=1e-5, out_dtype=dt)
             wg, bg, gbn = L[tb + "ff1"]
             if self.bf16:
                 gg = self._linear(a, wg, bg, geglu_bn=gbn)
             else:
                 gg = ops.geglu(self._linear(a, wg, bg))
-            t = self._linear(gg, *L[tb + "ff2"], residual=t)
+            # the last block's output only feeds proj_out as a GEMM operand: store it in the operand dtype
+            t = self._linear(gg, *L[tb + "ff2"], residual=t, trunk=(d != self.depth - 1))
         w, b = L[pre + "proj_out"]
-        return self._linear(t, w, b, residual=x).view(n, H, W, ch)
+        return self._linear(t, w, b, residual=x, trunk=True).view(n, H, W, ch)
 
     def _down(self, pre, x):
         w, b = self.L[pre + "op"]
         n, H, W, C = x.shape
         if self.bf16:
-            col = ops.im2col3x3(x, 2)                    # [n, OH, OW, 9C]
+            col = ops.im2col3x3(x, 2, out_dtype=self.dtype)      # [n, OH, OW, 9C]
             OH, OW = col.shape[1], col.shape[2]
-            return ops.gemm_tc([(col.view(-1, 9 * C), 1)], w, bias=b).view(n, OH, OW, -1)
+            return ops.gemm_tc([(col.view(-1, 9 * C), 1)], w, bias=b, out_dtype=torch.float32).view(n, OH, OW, -1)
         return ops.conv_direct(x, w, 3, 3, 2, 1, bias=b)
 
     def _up(self, pre, x):
         w, b = self.L[pre + "up"]
         if self.bf16:
-            return self._conv3(ops.upsample_nearest2x(x), w, b)
+            return self._conv3(ops.upsample_nearest2x(x, out_dtype=self.dtype), w, b, trunk=True)
         return ops.conv_direct(x, w, 3, 3, 1, 1, upsample=True, bias=b)
 
     # ------------------------------------------------------------------------------------------------
@@ -366,7 +378,7 @@ class UNetModel:
         def run(pre, layer, h, skip):
             kind = layer[0]
             if kind == "conv":
-                return self._conv3(h, *L[pre + "conv"])
+                return self._conv3(h, *L[pre + "conv"], trunk=True)
             if kind == "res":
                 return self._res(pre, layer, h, skip, emb_all)
             if kind == "st":
@@ -392,7 +404,7 @@ class UNetModel:
             if taps is not None:
                 taps["output_blocks.%d" % bi] = h
         g, b = L["out_norm"]
-        h = ops.groupnorm(h, g, b, 32, 1e-5, silu=True, scratch=self._gn_scratch)
+        h = ops.groupnorm(h, g, b, 32, 1e-5, silu=True, scratch=self._gn_scratch, out_dtype=self.dtype)
         nn_, H, W, _ = h.shape
         w, b = L["out_conv"]
         if self.bf16:
@@ -421,14 +433,16 @@ class UNetModel:
             self._forward_impl(sx, st_, repeat)  # warm-up: sets kernel attributes, fills the allocator
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
                 sout = self._forward_impl(sx, st_, repeat)
-            ent = (graph, sx, st_, sout)
+            ent = (graph, sx, st_, sout, _lib.launch_count() - n0)
             self._graphs[key] = ent
-        graph, sx, st_, sout = ent
+        graph, sx, st_, sout, nk = ent
         sx.copy_(x_nchw)
         st_.copy_(t)
         graph.replay()
+        self.replayed_launches += nk
         return sout
 
     def __call__(self, x, timesteps=None, context=None, y=None):

@@ -31,7 +31,7 @@ def test_abi_reports_errors_without_touching_the_gpu():
     lib = _lib.load()
     rc = lib.mdx_gemm_tc(None, None)
     assert rc == -22 and b"NULL" in lib.mdx_last_error()
-    rc = lib.mdx_layernorm(None, 0, 0, 0, 0.0, None, None, None, 0, 0, None)
+    rc = lib.mdx_layernorm(None, 0, 0, 0, 0.0, None, None, None, 0, 0, 0, None)
     assert rc == -22
 
 

@@ -48,6 +48,10 @@ def test_gemm_tc_dense(M, K, N):
     ref = a @ w.t() + bias + res
     out = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), bias=bias.cuda(), residual=res.cuda().bfloat16())
     assert rel_err(out, ref) < 1e-2
+    res32 = torch.randn(M, N, generator=g)  # fp32 residual trunk in, fp32 out
+    out = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), bias=bias.cuda(), residual=res32.cuda(),
+                      out_dtype=torch.float32)
+    assert rel_err(out, a @ w.t() + bias + res32) < 1e-4
     out32 = ops.gemm_tc([(a.cuda().bfloat16(), 1)], w.cuda().bfloat16(), out_dtype=torch.float32)
     assert rel_err(out32, a @ w.t()) < 1e-4
 
@@ -194,6 +198,12 @@ def test_groupnorm(dtype, tol, C1, C2, HW, silu, eps):
     out = ops.groupnorm(x1.cuda().to(dtype), gamma.cuda(), beta.cuda(), 32, eps, silu=silu,
                         x2=x2.cuda().to(dtype) if x2 is not None else None)
     assert rel_err(out, ref) < tol
+    if dtype == torch.float32:
+        # fp32 residual trunk -> bf16 GEMM operand, plus the raw bf16 copy for the 1x1 skip conv
+        out16, raw = ops.groupnorm(x1.cuda(), gamma.cuda(), beta.cuda(), 32, eps, silu=silu,
+                                   x2=x2.cuda() if x2 is not None else None, out_dtype=torch.bfloat16, raw_copy=True)
+        assert out16.dtype == torch.bfloat16 and rel_err(out16, ref) < 1e-2
+        assert torch.equal(raw.cpu(), xc.to(torch.bfloat16))
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
@@ -209,6 +219,9 @@ def test_layernorm(dtype, tol, C):
     ref = F.layer_norm(x, (C,), gamma, beta, 1e-5)
     out = ops.layernorm(x.cuda().to(dtype), gamma.cuda(), beta.cuda(), 1e-5)
     assert rel_err(out, ref) < tol
+    if dtype == torch.float32:
+        out16 = ops.layernorm(x.cuda(), gamma.cuda(), beta.cuda(), 1e-5, out_dtype=torch.bfloat16)
+        assert out16.dtype == torch.bfloat16 and rel_err(out16, ref) < 1e-2
 
 
 # ------------------------------------------------------------------ attention
@@ -278,6 +291,9 @@ def test_layout_movers(dtype):
     unf = F.unfold(z.float().permute(0, 3, 1, 2), 3, padding=1, stride=2)  # [n, C*9, L], order (c, r, s)
     unf = unf.view(2, 16, 9, 4, 4).permute(0, 3, 4, 2, 1).reshape(2, 4, 4, 9 * 16)
     assert torch.equal(col.cpu().float(), unf)
+    if dtype == torch.float32:  # converting variants used by the fp32 trunk
+        assert torch.equal(ops.im2col3x3(z.cuda(), 2, out_dtype=torch.bfloat16).cpu(), unf.to(torch.bfloat16))
+        assert torch.equal(ops.upsample_nearest2x(y.cuda(), out_dtype=torch.bfloat16).cpu(), up.cpu().to(torch.bfloat16))
     assert torch.equal(ops.cast(z.cuda(), torch.float32).cpu(), z.float())
 
 
