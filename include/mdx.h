@@ -121,6 +121,24 @@ int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64
                   void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
                   double* stats_scratch, void* stream);
 
+/* GroupNorm without caller scratch.  (No counterpart in the reference: MindSpore hands its kernels a workspace;
+ * this exists for callers of THIS library that cannot provide one.)
+ * Same operands and dtype pairs as mdx_groupnorm, minus stats_scratch: the per-group sums live in a fixed
+ * 256 KiB device array inside the library (present on every GPU that loads it, for the life of the process).
+ * Meant for call sites that cannot allocate device memory when they reach the norm — e.g. a framework custom-op
+ * body that receives only its input/output addresses and a stream, or a thread that must stay out of the
+ * allocator because the host framework's memory pool is frozen.
+ *  - limit: n * groups <= 16384, otherwise -22 with a message pointing back at mdx_groupnorm;
+ *  - the first call on each device resolves the array's device address (cudaGetSymbolAddress, with that device
+ *    current); issue that first call before beginning any stream capture;
+ *  - never calls cudaMalloc/cudaFree or any allocating routine;
+ *  - every call on a device shares the array: each call clears what it uses on `stream` before accumulating,
+ *    so consecutive calls on one stream are fine, but calls that may overlap on the GPU race with each other. */
+int mdx_groupnorm_noalloc(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
+                          int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma, const float* beta,
+                          int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype,
+                          int32_t out_dtype, void* stream);
+
 /* LayerNorm over the last dim of [rows, C] (ldx/ldo row strides). Replaces nn.LayerNorm([dim], epsilon=1e-5)
  * (attention.py:176-178).  Biased variance, fp32 statistics, one warp per row.  dtype pairs as mdx_groupnorm. */
 int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,

@@ -65,6 +65,8 @@ SIGNATURES = {
     "mdx_conv_direct": (c_int, [ctypes.POINTER(ConvArgs), c_p]),
     "mdx_groupnorm": (c_int, [c_p, c_i64, c_int, c_p, c_i64, c_int, c_int, c_int, c_int, c_f, c_p, c_p, c_int, c_p,
                               c_i64, c_p, c_i64, c_int, c_int, c_p, c_p]),
+    "mdx_groupnorm_noalloc": (c_int, [c_p, c_i64, c_int, c_p, c_i64, c_int, c_int, c_int, c_int, c_f, c_p, c_p, c_int,
+                                      c_p, c_i64, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_layernorm": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_p, c_p, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_attention": (c_int, [c_p, c_i64, c_p, c_i64, c_p, c_i64, c_p, c_i64, c_int, c_int, c_int, c_int, c_int, c_f,
                               c_int, c_p]),

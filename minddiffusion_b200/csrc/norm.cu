@@ -279,3 +279,70 @@ extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C
   MDX_CHECK_LAUNCH();
   return MDX_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// mdx_groupnorm_noalloc: GroupNorm for callers that cannot hand us a scratch buffer.
+//
+// mdx_groupnorm needs n*groups*2 doubles of device scratch for the per-group sums, and expects the caller to
+// own them.  Some callers have no way to obtain device memory at the point of the call: a custom-op body that
+// a framework invokes with nothing but its input/output addresses and a stream (the MindSpore `Custom` aot
+// form INTEGRATION.md describes gets no workspace), a host thread that must not touch the allocator because
+// the framework's memory pool is frozen, or code that runs inside a region where cudaMalloc is forbidden.
+// For them the statistics live in the fixed array below, which is part of the library image: every GPU that
+// loads libmdx_b200.so carries MDX_GN_NOALLOC_MAX_PAIRS * 16 bytes (256 KiB) of it until the process exits.
+//
+// The array's name is only a host-side handle in host code, so its device address is looked up with
+// cudaGetSymbolAddress, once per device, with that device current, the first time the entry point is called
+// there.  That first call does the lookup (it may also trigger the lazy load of this module), so make it before
+// starting any stream capture.  Nothing here allocates: no cudaMalloc / cudaFree, no library routine that does.
+//
+// All calls on a device share the one array and it keeps whatever the previous call left in it.  Each call
+// clears the part it uses (on the stream) before accumulating, so back-to-back calls on one stream are safe;
+// two calls that can overlap on the GPU (different streams, no ordering between them) race on the array and
+// must not be issued.
+// ---------------------------------------------------------------------------------------------------------
+#define MDX_GN_NOALLOC_MAX_PAIRS 16384  /* n * groups must not exceed this */
+static __device__ __align__(256) double g_gn_noalloc_stats[MDX_GN_NOALLOC_MAX_PAIRS * 2];
+
+#include <mutex>
+
+namespace {
+constexpr int kMaxDevices = 64;
+double* g_gn_noalloc_ptr[kMaxDevices] = {nullptr};
+std::mutex g_gn_noalloc_mu;
+
+// Device address of g_gn_noalloc_stats on the CURRENT device (resolved once per device).
+int gn_noalloc_scratch(double** out) {
+  int dev = -1;
+  MDX_CHECK_CUDA(cudaGetDevice(&dev));
+  MDX_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "mdx_groupnorm_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_gn_noalloc_mu);
+  if (g_gn_noalloc_ptr[dev] == nullptr) {
+    double* p = nullptr;
+    MDX_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_noalloc_stats));
+    MDX_CHECK_ARG(p != nullptr, "mdx_groupnorm_noalloc: cudaGetSymbolAddress returned NULL");
+    g_gn_noalloc_ptr[dev] = p;
+  }
+  *out = g_gn_noalloc_ptr[dev];
+  return MDX_OK;
+}
+}  // namespace
+
+extern "C" int mdx_groupnorm_noalloc(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2,
+                                     int32_t C2, int32_t n, int32_t HW, int32_t groups, float eps,
+                                     const float* gamma, const float* beta, int32_t silu, void* out, int64_t ldo,
+                                     void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
+                                     void* stream) {
+  MDX_CHECK_ARG(n > 0 && groups > 0, "mdx_groupnorm_noalloc: empty problem");
+  MDX_CHECK_ARG((long long)n * groups <= MDX_GN_NOALLOC_MAX_PAIRS,
+                "mdx_groupnorm_noalloc: n*groups = %lld exceeds the built-in scratch (%d); use mdx_groupnorm with "
+                "caller-provided scratch",
+                (long long)n * groups, MDX_GN_NOALLOC_MAX_PAIRS);
+  double* scratch = nullptr;
+  int rc = gn_noalloc_scratch(&scratch);
+  if (rc != MDX_OK) return rc;
+  // mdx_groupnorm zeroes the n*groups*2 doubles it is about to use (cudaMemsetAsync on `stream`) before the
+  // statistics kernel accumulates into them, so the previous call's contents never leak into this one.
+  return mdx_groupnorm(x1, ld1, C1, x2, ld2, C2, n, HW, groups, eps, gamma, beta, silu, out, ldo, raw_copy, ldraw,
+                       in_dtype, out_dtype, scratch, stream);
+}
