@@ -254,8 +254,8 @@ def run_b200(a):
     unet.forward_nhwc(x_dev, t_probe, repeat=2)
     torch.cuda.synchronize()
     ops.GEMM_TC_PROFILE = None
-    flops = sum(f for f, _, _ in prof)
-    gemm_ms = sum(s.elapsed_time(e) for _, s, e in prof)
+    flops = sum(p_[0] for p_ in prof)
+    gemm_ms = sum(p_[1].elapsed_time(p_[2]) for p_ in prof)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))

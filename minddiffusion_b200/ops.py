@@ -123,7 +123,9 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
         e0.record()
         check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
         e1.record()
-        GEMM_TC_PROFILE.append((2.0 * M * N * ktot, e0, e1))
+        GEMM_TC_PROFILE.append((2.0 * M * N * ktot, e0, e1, (M, N, ktot, [t for _, t in segs], str(out.dtype)[6:],
+                                                               None if residual is None else str(residual.dtype)[6:],
+                                                               bool(geglu), rowbias is not None)))
         return out
     check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
     return out
