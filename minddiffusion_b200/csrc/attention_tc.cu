@@ -1,0 +1,404 @@
+// Flash attention on the 5th-generation tensor cores (tcgen05 + TMEM) for head dim 64 — the shape of every
+// attention layer of the stablediffusionv2 UNet (num_head_channels: 64, configs/v2-inference.yaml:31).
+// Reference semantics: CrossAttention.construct, ldm/modules/attention.py:134-152:  softmax(q k^T * d^-1/2) v.
+//
+// One CTA = 128 queries of one (batch, head); keys/values stream through in tiles of 128.
+//   warp 0 : TMA producer   Q once, then K and V tiles (3-D boxes cut straight out of the fused [B, N, 3C] / [B, L, 2C]
+//                           projection buffers, 128-byte swizzle), two mbarrier rings
+//   warp 1 : MMA issuer     S_j = Q K_j^T   (M128 x N128 x K64, both operands K-major)        -> TMEM S[j&1]
+//                           O_j = P_j V_j   (M128 x N64 x K128, A = P from smem, B = V MN-major) -> TMEM O[j&1]
+//   warp 2 : TMEM allocate / free (512 columns: 2 x 128 for S, 2 x 64 for O)
+//   warps 4-11: softmax, two warpgroups ping-ponging over key tiles (group g owns tiles g, g+2, ...).  Thread =
+//                           query row (TMEM lane), so row max / row sum need no shuffles.  Two passes over S in TMEM
+//                           (max, then exp2 + sum), P written as bf16 into a 128B-swizzled smem operand, running
+//                           output kept in fp32 registers: O <- (O + O_prev) * alpha, one tile late so that the P V
+//                           MMA overlaps the next softmax; the two groups' (max, sum, O) are merged at the end.
+// Keys beyond Nk are masked to -inf (K/V rows there are zero-filled by TMA); query rows beyond Nq are not stored.
+#include "common.cuh"
+#include <atomic>
+
+extern std::atomic<long long> g_mdx_launches;
+
+namespace {
+
+constexpr int AT_BM = 128;   // queries per CTA
+constexpr int AT_BN = 128;   // keys per tile
+constexpr int AT_D = 64;
+constexpr int AT_KS = 3;     // K ring depth
+constexpr int AT_VS = 3;     // V ring depth
+constexpr int TILE_BYTES = 128 * 64 * 2;  // 16 KiB: one [128 x 64] bf16 operand block
+
+struct AttnTcP {
+  int Nq, Nk;
+  float sl2;  // scale * log2(e)
+  bf16* o;
+  long long ldo;
+};
+
+// smem map (offsets from the 1024-aligned base)
+constexpr int OFF_Q = 0;
+constexpr int OFF_K = OFF_Q + TILE_BYTES;
+constexpr int OFF_V = OFF_K + AT_KS * TILE_BYTES;
+constexpr int OFF_P = OFF_V + AT_VS * TILE_BYTES;          // 2 buffers x 2 K-blocks
+constexpr int OFF_BAR = OFF_P + 2 * 2 * TILE_BYTES;
+constexpr int OFF_XML = OFF_BAR + 512;
+constexpr int AT_SMEM = OFF_XML + 1024 + 1024;
+
+__device__ __forceinline__ void tma_load_3d(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// MN-major operand (V as B of the P V product): rows of 64 elements (128 B) along N, 8-row swizzle atoms along K,
+// 1024 B between atoms (SBO).  Same bit layout as umma_desc_sw128; LBO is unused because N spans one atom.
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr) { return umma_desc_sw128(smem_addr); }
+// instruction descriptor: bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16)
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_bmn(int M, int N) { return umma_idesc_bf16(M, N) | (1u << 16); }
+
+__global__ void __launch_bounds__(384, 1)
+attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+               const __grid_constant__ CUtensorMap tmV, const AttnTcP p) {
+  extern __shared__ uint8_t at_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* q_full = bars;                 // 1
+  uint64_t* k_full = bars + 1;             // AT_KS
+  uint64_t* k_empty = k_full + AT_KS;      // AT_KS
+  uint64_t* v_full = k_empty + AT_KS;      // AT_VS
+  uint64_t* v_empty = v_full + AT_VS;      // AT_VS
+  uint64_t* s_full = v_empty + AT_VS;      // 2
+  uint64_t* s_empty = s_full + 2;          // 2
+  uint64_t* p_full = s_empty + 2;          // 2
+  uint64_t* p_empty = p_full + 2;          // 2
+  uint64_t* o_full = p_empty + 2;          // 2
+  uint64_t* o_empty = o_full + 2;          // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * AT_BM;
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int T = (p.Nk + AT_BN - 1) / AT_BN;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
+    for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);  mbar_init(&s_empty[i], 128);
+      mbar_init(&p_full[i], 128); mbar_init(&p_empty[i], 1);
+      mbar_init(&o_full[i], 1);  mbar_init(&o_empty[i], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t TM_S = tmem_base;          // S[sb] at columns sb*128
+  const uint32_t TM_O = tmem_base + 256;    // O[ob] at columns 256 + ob*64
+
+  if (warp == 0) {
+    if (elect_one()) {
+      // ===================== TMA producer =====================
+      mbar_arrive_expect_tx(q_full, TILE_BYTES);
+      tma_load_3d(smem + OFF_Q, &tmQ, q_full, head * AT_D, q0, b);
+      for (int j = 0; j < T; ++j) {
+        const int ks = j % AT_KS, vs = j % AT_VS;
+        mbar_wait(&k_empty[ks], ((j / AT_KS) & 1) ^ 1);
+        mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
+        tma_load_3d(smem + OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], head * AT_D, j * AT_BN, b);
+        mbar_wait(&v_empty[vs], ((j / AT_VS) & 1) ^ 1);
+        mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+        tma_load_3d(smem + OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], head * AT_D, j * AT_BN, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+      constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+      const uint32_t q_base = smem_u32(smem + OFF_Q);
+      auto issue_pv = [&](int i) {
+        const int pb = i & 1, vs = i % AT_VS, ob = i & 1;
+        mbar_wait(&p_full[pb], (i >> 1) & 1);
+        mbar_wait(&v_full[vs], (i / AT_VS) & 1);
+        mbar_wait(&o_empty[ob], ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t p_base = smem_u32(smem + OFF_P + pb * 2 * TILE_BYTES);
+        const uint32_t v_base = smem_u32(smem + OFF_V + vs * TILE_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < AT_BN / 16; ++kk) {
+          const uint32_t a_addr = p_base + (kk >> 2) * TILE_BYTES + (kk & 3) * 32;  // K-block of 64 keys, 32 B per K16
+          const uint32_t b_addr = v_base + kk * 16 * 128;                          // 16 key rows of 128 B
+          umma_bf16(TM_O + ob * AT_D, umma_desc_sw128(a_addr), umma_desc_sw128_mn(b_addr), idesc_o, kk != 0 ? 1u : 0u);
+        }
+        umma_commit(&o_full[ob]);
+        umma_commit(&v_empty[vs]);
+        umma_commit(&p_empty[pb]);
+      };
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < T; ++j) {
+        const int ks = j % AT_KS, sb = j & 1;
+        mbar_wait(&k_full[ks], (j / AT_KS) & 1);
+        mbar_wait(&s_empty[sb], ((j >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t k_base = smem_u32(smem + OFF_K + ks * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < AT_D / 16; ++k)
+          umma_bf16(TM_S + sb * AT_BN, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s,
+                    k != 0 ? 1u : 0u);
+        umma_commit(&s_full[sb]);
+        umma_commit(&k_empty[ks]);
+        if (j >= 1) issue_pv(j - 1);
+      }
+      issue_pv(T - 1);
+    }
+  } else if (warp >= 4) {
+    // ===================== softmax + output =====================
+    // Two warpgroups ping-pong over the key tiles: group g owns tiles j = g, g+2, ... and with them S[g], P[g],
+    // O[g].  Each keeps its own running (max, sum, O) — two independent online-softmax streams — merged once at
+    // the end.  Two warps per scheduler hide the TMEM-load / MUFU latencies that a single warp cannot.
+    const int g = (warp - 4) >> 2;
+    const int qw = warp & 3;
+    const int row = qw * 32 + lane;                         // query row in the tile == TMEM lane
+    const uint32_t lane_off = (uint32_t)(qw * 32) << 16;
+    float o_acc[AT_D];
+#pragma unroll
+    for (int i = 0; i < AT_D; ++i) o_acc[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const float c = p.sl2;
+    uint8_t* prow = smem + OFF_P + g * 2 * TILE_BYTES + row * 128;
+    const int swz = row & 7;
+    const uint32_t ts = TM_S + lane_off + g * AT_BN;
+    const uint32_t to = TM_O + lane_off + g * AT_D;
+
+    int it = 0;  // this group's iteration count (phase bit of its barriers)
+    for (int j = g; j < T; j += 2, ++it) {
+      mbar_wait(&s_full[g], it & 1);
+      tc_fence_after();
+      const int key0 = j * AT_BN;
+      // ---- pass 1: row max (four independent chains: one warp per scheduler cannot hide a 32-deep one) ----
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll 1
+      for (int cc = 0; cc < AT_BN / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(ts + cc * 32, r);
+        tmem_ld_wait();
+        const int kb = key0 + cc * 32;
+        if (kb + 32 <= p.Nk) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            mx0 = fmaxf(mx0, __uint_as_float(r[i]));
+            mx1 = fmaxf(mx1, __uint_as_float(r[i + 1]));
+            mx2 = fmaxf(mx2, __uint_as_float(r[i + 2]));
+            mx3 = fmaxf(mx3, __uint_as_float(r[i + 3]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (kb + i < p.Nk) mx0 = fmaxf(mx0, __uint_as_float(r[i]));
+        }
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      const float m_new = fmaxf(m_run, mx);
+      const float alpha = ex2_approx((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
+      const float msc = m_new * c;
+      // ---- pass 2: p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
+      mbar_wait(&p_empty[g], (it & 1) ^ 1);
+      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+      for (int cc = 0; cc < AT_BN / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(ts + cc * 32, r);
+        tmem_ld_wait();
+        const int kb = key0 + cc * 32;
+        const bool full = kb + 32 <= p.Nk;
+        uint8_t* pblk = prow + (cc >> 1) * TILE_BYTES;       // K-block of 64 keys
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {                     // 4 chunks of 8 keys (16 B)
+          uint32_t pk[4];
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int i = ch * 8 + h * 2;
+            float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
+            if (!full) {
+              if (kb + i >= p.Nk) s0 = -INFINITY;
+              if (kb + i + 1 >= p.Nk) s1 = -INFINITY;
+            }
+            const float p0 = ex2_approx(fmaf(s0, c, -msc));
+            const float p1 = ex2_approx(fmaf(s1, c, -msc));
+            rs4[h] += p0 + p1;
+            pk[h] = pack_bf16x2(p0, p1);
+          }
+          const int chunk = (cc & 1) * 4 + ch;               // 16-byte chunk index inside the 128-byte row
+          *reinterpret_cast<uint4*>(pblk + ((chunk ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+      }
+      l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
+      m_run = m_new;
+      tc_fence_before();
+      fence_proxy_async_smem();          // generic-proxy stores of P -> visible to the tensor core (async proxy)
+      mbar_arrive(&p_full[g]);
+      mbar_arrive(&s_empty[g]);
+      // ---- deferred accumulation of this group's previous tile: O <- (O + O_prev) * alpha ----
+      if (it >= 1) {
+        mbar_wait(&o_full[g], (it - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < AT_D / 32; ++cc) {
+          uint32_t r[32];
+          tmem_ld32(to + cc * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = (o_acc[cc * 32 + i] + __uint_as_float(r[i])) * alpha;
+        }
+        tc_fence_before();
+        mbar_arrive(&o_empty[g]);
+      }
+    }
+    // this group's last P V
+    if (it >= 1) {
+      mbar_wait(&o_full[g], (it - 1) & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int cc = 0; cc < AT_D / 32; ++cc) {
+        uint32_t r[32];
+        tmem_ld32(to + cc * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] += __uint_as_float(r[i]);
+      }
+      tc_fence_before();
+    }
+    // ---- merge the two streams: group 1 parks (m, l, O) in its own (now idle) P buffer, group 0 combines ----
+    float* xch = reinterpret_cast<float*>(smem + OFF_P + 2 * TILE_BYTES);   // P[1]: 32 KiB = 128 rows x 64 fp32
+    float* xml = reinterpret_cast<float*>(smem + OFF_XML);                  // 128 x {m, l}
+    if (g == 1) {
+#pragma unroll
+      for (int i = 0; i < AT_D; ++i) xch[i * AT_BM + row] = o_acc[i];     // column-major: conflict-free
+      xml[row * 2] = m_run;
+      xml[row * 2 + 1] = l_run;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (g == 0) {
+      const float m1 = xml[row * 2], l1 = xml[row * 2 + 1];
+      const float m = fmaxf(m_run, m1);
+      const float w0 = ex2_approx((m_run - m) * c);
+      const float w1 = (m1 == -INFINITY) ? 0.f : ex2_approx((m1 - m) * c);
+      const float inv = 1.f / (l_run * w0 + l1 * w1);
+      if (q0 + row < p.Nq) {
+        bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * AT_D;
+#pragma unroll
+        for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = (o_acc[v8 * 8 + i] * w0 + xch[(v8 * 8 + i) * AT_BM + row] * w1) * inv;
+          uint4 u;
+          u.x = pack_bf16x2(f[0], f[1]);
+          u.y = pack_bf16x2(f[2], f[3]);
+          u.z = pack_bf16x2(f[4], f[5]);
+          u.w = pack_bf16x2(f[6], f[7]);
+          *reinterpret_cast<uint4*>(orow + v8 * 8) = u;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn at_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// [batch, rows, heads*64] bf16 view with row stride ld: box = 64 channels x 128 rows x 1 batch
+int make_map_qkv(CUtensorMap* m, const void* ptr, long long ld, int width, int rows, int batch) {
+  EncodeTiledFn enc = at_encode_fn();
+  if (!enc) {
+    mdx_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return MDX_ERR_CUDA;
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)width, (cuuint64_t)rows, (cuuint64_t)batch};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows * ld * 2};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t es[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mdx_set_error("cuTensorMapEncodeTiled(attention) failed with CUresult %d", (int)r);
+    return MDX_ERR_CUDA;
+  }
+  return MDX_OK;
+}
+
+}  // namespace
+
+// Internal entry (called by mdx_attention for bf16, d == 64).
+int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                         void* o, long long ldo, int batch, int heads, int Nq, int Nk, float scale,
+                         cudaStream_t st) {
+  CUtensorMap mq, mk, mv;
+  int rc;
+  if ((rc = make_map_qkv(&mq, q, ldq, heads * AT_D, Nq, batch))) return rc;
+  if ((rc = make_map_qkv(&mk, k, ldk, heads * AT_D, Nk, batch))) return rc;
+  if ((rc = make_map_qkv(&mv, v, ldv, heads * AT_D, Nk, batch))) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    attr_set = true;
+  }
+  AttnTcP p;
+  p.Nq = Nq; p.Nk = Nk; p.sl2 = scale * 1.4426950408889634f;
+  p.o = reinterpret_cast<bf16*>(o); p.ldo = ldo;
+  dim3 grid((Nq + AT_BM - 1) / AT_BM, heads, batch);
+  attn_tc_kernel<<<grid, 384, AT_SMEM, st>>>(mq, mk, mv, p);
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}

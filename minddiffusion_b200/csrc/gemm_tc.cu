@@ -46,13 +46,18 @@ struct TcParams {
 
 template <int BN> struct TcCfg {
   static constexpr int B_STAGE_BYTES = BN * BK * 2;
-  static constexpr int STAGES = (BN >= 256) ? 4 : (BN >= 160 ? 6 : (BN >= 128 ? 6 : 8));
+  static constexpr int STAGES = (BN >= 256) ? 4 : (BN >= 160 ? 5 : (BN >= 128 ? 5 : 7));
   static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
-  static constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 256 /*barriers*/ + 1024 /*align*/;
+  static constexpr int EPI_WARPS = (BN >= 256) ? 4 : 8;      // 4 TMEM lane quadrants x {1,2} column parities
+  static constexpr int THREADS = 128 + 32 * EPI_WARPS;
+  static constexpr int STG_LD = 36;                           // floats per staging row (32 + 4 pad, 16-B aligned)
+  static constexpr int STAGING_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 256;
+  static constexpr int SMEM_BYTES = STAGING_OFF + EPI_WARPS * 32 * STG_LD * 4 + 1024 /*align*/;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 
 template <int BN>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(TcCfg<BN>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
@@ -84,7 +89,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 128);
+      mbar_init(&tempty[i], 32 * Cfg::EPI_WARPS);
     }
     fence_mbar_init();
   }
@@ -167,11 +172,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int qw = warp & 3;  // TMEM lane quadrant this warp may read
+    // Phase 1 (row-owner layout, what tcgen05.ld gives): thread `lane` of the warp holds accumulator row
+    //   32*q + lane; GEGLU's value*gelu(gate) is formed here.  The chunk (<= 32 output columns) goes to a
+    //   per-warp smem staging tile.
+    // Phase 2 (coalesced layout): 8 lanes cover 32 consecutive columns of one row, 4 rows per pass, so global
+    //   reads of the residual and writes of the output are contiguous 128-byte (fp32) / 64-byte (bf16) segments.
+    constexpr int NEW = Cfg::EPI_WARPS;
+    const int ew = warp - 4;
+    const int qw = ew & 3;                 // TMEM lane quadrant this warp may read
+    const int cpar = ew >> 2;              // with 8 epilogue warps: even / odd chunks
     const int row = qw * 32 + lane;
     const int xl = row % p.tw;
     const int yl = (row / p.tw) % p.th;
     const int nl = row / (p.tw * p.th);
+    float* stg = reinterpret_cast<float*>(smem + Cfg::STAGING_OFF) + ew * (32 * Cfg::STG_LD);
+    const int sub_row = lane >> 3;         // phase 2: row within a pass of 4
+    const int c4 = (lane & 7) * 4;         // phase 2: first of this lane's 4 columns inside the chunk
+    constexpr int OUTW = BN;               // output columns per tile (GEGLU: BN/2)
     uint32_t iter = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++iter) {
       const uint32_t as = iter & 1;
@@ -182,119 +199,107 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const int y = ((m_tile / p.tiles_x) % p.tiles_y) * p.th + yl;
       const int n = (m_tile / tiles_per_img_grid) * p.tn + nl;
       const bool valid = (x < p.W) && (y < p.H) && (n < p.n_img);
-      const long long pix = ((long long)n * p.H + y) * p.W + x;
+      const long long pix_own = valid ? ((long long)n * p.H + y) * p.W + x : -1;
 
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + as * BN;
 
-      if (!p.geglu) {
+      // pixel index of the row each lane serves in each phase-2 pass (constant over the tile's chunks)
+      long long pixs[8];
+#pragma unroll
+      for (int pass = 0; pass < 8; ++pass) pixs[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 4 + sub_row);
+
+      const int outw = p.geglu ? OUTW / 2 : OUTW;            // output columns this tile produces
+      const int n_out = p.geglu ? p.N / 2 : p.N;             // output columns of the whole GEMM
+      const int ocol_tile = n_tile * outw;
+      const int nchunks = (outw + 31) / 32;
 #pragma unroll 1
-        for (int c = 0; c < BN / 16; ++c) {
-          const int col0 = n_tile * BN + c * 16;
-          if (col0 >= p.N) break;
-          uint32_t r[16];
-          tmem_ld16(taddr + c * 16, r);
-          tmem_ld_wait();
-          if (valid) {
-            float v[16];
+      for (int c = cpar; c < nchunks; c += (NEW / 4)) {
+        const int cw = min(32, outw - c * 32);               // 32 or 16
+        const int ocol0 = ocol_tile + c * 32;
+        if (ocol0 >= n_out) break;
+        // ---- prefetch (coalesced layout): everything phase 2 adds that does not depend on the accumulator.
+        // Issued before the TMEM load so that the 8 x 512 B reads per warp are in flight together. ----
+        const bool col_ok = c4 < cw && (ocol0 + c4) < n_out;
+        float4 radd[8];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-            if (p.bias) {
-              const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                float4 b = __ldg(bp + i);
-                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+        for (int pass = 0; pass < 8; ++pass) {
+          float4 acc4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          const long long pix = pixs[pass];
+          if (col_ok && pix >= 0) {
+            if (p.residual) {
+              if (p.res_f32) {
+                acc4 = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + pix * p.ldr + ocol0 + c4));
+              } else {
+                const uint2 u = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ldr + ocol0 + c4));
+                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+                acc4 = make_float4(f0.x, f0.y, f1.x, f1.y);
               }
             }
             if (p.rowbias) {
-              const float4* bp = reinterpret_cast<const float4*>(p.rowbias + (long long)n * p.ld_rowbias + col0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                float4 b = __ldg(bp + i);
-                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
-              }
+              const int img = (int)(pix / ((long long)p.H * p.W));
+              const float4 rb = __ldg(reinterpret_cast<const float4*>(p.rowbias + (long long)img * p.ld_rowbias + ocol0 + c4));
+              acc4.x += rb.x; acc4.y += rb.y; acc4.z += rb.z; acc4.w += rb.w;
             }
-            if (p.residual && p.res_f32) {
-              const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + pix * p.ldr + col0);
+          }
+          radd[pass] = acc4;
+        }
+        // ---- phase 1 ----
+        float v[32];
+        if (!p.geglu) {
+          uint32_t r0[16], r1[16];
+          tmem_ld16(taddr + c * 32, r0);
+          if (cw > 16) tmem_ld16(taddr + c * 32 + 16, r1);
+          tmem_ld_wait();
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                float4 b = __ldg(rp + i);
-                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+          for (int i = 0; i < 16; ++i) { v[i] = __uint_as_float(r0[i]); v[16 + i] = cw > 16 ? __uint_as_float(r1[i]) : 0.f; }
+        } else {
+          constexpr int HALF = BN / 2;
+#pragma unroll
+          for (int hsel = 0; hsel < 2; ++hsel) {
+            if (hsel * 16 < cw) {
+              uint32_t rv[16], rg[16];
+              tmem_ld16(taddr + c * 32 + hsel * 16, rv);
+              tmem_ld16(taddr + HALF + c * 32 + hsel * 16, rg);
+              tmem_ld_wait();
+              const int bcol_v = n_tile * BN + c * 32 + hsel * 16;   // bias is packed like the weight rows
+              const int bcol_g = bcol_v + HALF;
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                float a = __uint_as_float(rv[i]);
+                float g = __uint_as_float(rg[i]);
+                if (p.bias) { a += __ldg(p.bias + bcol_v + i); g += __ldg(p.bias + bcol_g + i); }
+                v[hsel * 16 + i] = a * gelu_tanh_fast(g);
               }
-            } else if (p.residual) {
-              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ldr + col0);
-#pragma unroll
-              for (int i = 0; i < 2; ++i) {
-                uint4 u = __ldg(rp + i);
-                float2 f;
-                f = unpack_bf16x2(u.x); v[8 * i] += f.x; v[8 * i + 1] += f.y;
-                f = unpack_bf16x2(u.y); v[8 * i + 2] += f.x; v[8 * i + 3] += f.y;
-                f = unpack_bf16x2(u.z); v[8 * i + 4] += f.x; v[8 * i + 5] += f.y;
-                f = unpack_bf16x2(u.w); v[8 * i + 6] += f.x; v[8 * i + 7] += f.y;
-              }
-            }
-            if (p.out_f32) {
-              float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + col0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             } else {
-              uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + col0);
 #pragma unroll
-              for (int i = 0; i < 2; ++i) {
-                uint4 u;
-                u.x = pack_bf16x2(v[8 * i], v[8 * i + 1]);
-                u.y = pack_bf16x2(v[8 * i + 2], v[8 * i + 3]);
-                u.z = pack_bf16x2(v[8 * i + 4], v[8 * i + 5]);
-                u.w = pack_bf16x2(v[8 * i + 6], v[8 * i + 7]);
-                op[i] = u;
-              }
+              for (int i = 0; i < 16; ++i) v[hsel * 16 + i] = 0.f;
             }
           }
         }
-      } else {
-        // GEGLU: tile columns [0, BN/2) are "value", [BN/2, BN) the matching "gate" columns.
-        constexpr int HALF = BN / 2;
-        const int n_out = p.N / 2;
-#pragma unroll 1
-        for (int c = 0; c < HALF / 16; ++c) {
-          const int ocol0 = n_tile * HALF + c * 16;
-          if (ocol0 >= n_out) break;
-          uint32_t rv[16], rg[16];
-          tmem_ld16(taddr + c * 16, rv);
-          tmem_ld16(taddr + HALF + c * 16, rg);
-          tmem_ld_wait();
-          if (valid) {
-            float v[16];
-            const int bcol_v = n_tile * BN + c * 16;         // bias is packed like the weight rows
-            const int bcol_g = n_tile * BN + HALF + c * 16;
+        __syncwarp();  // previous chunk's phase-2 reads of the staging tile are done
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              float a = __uint_as_float(rv[i]);
-              float g = __uint_as_float(rg[i]);
-              if (p.bias) {
-                a += __ldg(p.bias + bcol_v + i);
-                g += __ldg(p.bias + bcol_g + i);
-              }
-              v[i] = a * gelu_tanh_f(g);
-            }
-            if (p.out_f32) {
-              float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0);
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(stg + lane * Cfg::STG_LD + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        // ---- phase 2 ----
+        float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (col_ok && p.bias && !p.geglu) bz = __ldg(reinterpret_cast<const float4*>(p.bias + ocol0 + c4));
 #pragma unroll
-              for (int i = 0; i < 4; ++i) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            } else {
-              uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + ocol0);
-#pragma unroll
-              for (int i = 0; i < 2; ++i) {
-                uint4 u;
-                u.x = pack_bf16x2(v[8 * i], v[8 * i + 1]);
-                u.y = pack_bf16x2(v[8 * i + 2], v[8 * i + 3]);
-                u.z = pack_bf16x2(v[8 * i + 4], v[8 * i + 5]);
-                u.w = pack_bf16x2(v[8 * i + 6], v[8 * i + 7]);
-                op[i] = u;
-              }
-            }
+        for (int pass = 0; pass < 8; ++pass) {
+          const int r = pass * 4 + sub_row;
+          const long long pix = pixs[pass];
+          if (!col_ok || pix < 0) continue;
+          float4 o = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + c4);
+          o.x += bz.x + radd[pass].x; o.y += bz.y + radd[pass].y; o.z += bz.z + radd[pass].z; o.w += bz.w + radd[pass].w;
+          if (p.out_f32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0 + c4) = o;
+          } else {
+            uint2 u;
+            u.x = pack_bf16x2(o.x, o.y);
+            u.y = pack_bf16x2(o.z, o.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + ocol0 + c4) = u;
           }
         }
       }
@@ -410,7 +415,7 @@ int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p,
     attr_set = true;
   }
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  gemm_tc_kernel<BN><<<grid, 256, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, p);
+  gemm_tc_kernel<BN><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, p);
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;
