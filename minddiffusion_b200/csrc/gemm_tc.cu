@@ -213,6 +213,60 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const int outw = p.geglu ? OUTW / 2 : OUTW;            // output columns this tile produces
       const int n_out = p.geglu ? p.N / 2 : p.N;             // output columns of the whole GEMM
       const int ocol_tile = n_tile * outw;
+      if (p.geglu) {
+        // GEGLU: per sub-chunk of 16 output columns stage [value16 | gate16], then in the coalesced layout
+        // (4 lanes x 4 columns per row, 8 rows per pass) form (value + bv) * gelu(gate + bg) and store bf16/fp32.
+        constexpr int HALF = BN / 2;
+        const int sr8 = lane >> 2, c4g = (lane & 3) * 4;
+        long long pix8[4];
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) pix8[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 8 + sr8);
+#pragma unroll 1
+        for (int sc = cpar; sc < HALF / 16; sc += (NEW / 4)) {
+          const int ocol0 = ocol_tile + sc * 16;
+          if (ocol0 >= n_out) break;
+          uint32_t rv[16], rg[16];
+          tmem_ld16(taddr + sc * 16, rv);
+          tmem_ld16(taddr + HALF + sc * 16, rg);
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f), bg = bv;
+          if (p.bias) {  // bias is packed like the weight rows: [value half | gate half] per tile
+            bv = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * BN + sc * 16 + c4g));
+            bg = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * BN + HALF + sc * 16 + c4g));
+          }
+          tmem_ld_wait();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            *reinterpret_cast<uint4*>(stg + lane * Cfg::STG_LD + 4 * j) = make_uint4(rv[4 * j], rv[4 * j + 1], rv[4 * j + 2], rv[4 * j + 3]);
+            *reinterpret_cast<uint4*>(stg + lane * Cfg::STG_LD + 16 + 4 * j) = make_uint4(rg[4 * j], rg[4 * j + 1], rg[4 * j + 2], rg[4 * j + 3]);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int pass = 0; pass < 4; ++pass) {
+            const int r = pass * 8 + sr8;
+            const long long pix = pix8[pass];
+            if (pix < 0) continue;
+            const float4 a = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + c4g);
+            const float4 g = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + 16 + c4g);
+            float4 o;
+            o.x = (a.x + bv.x) * gelu_tanh_fast(g.x + bg.x);
+            o.y = (a.y + bv.y) * gelu_tanh_fast(g.y + bg.y);
+            o.z = (a.z + bv.z) * gelu_tanh_fast(g.z + bg.z);
+            o.w = (a.w + bv.w) * gelu_tanh_fast(g.w + bg.w);
+            if (p.out_f32) {
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0 + c4g) = o;
+            } else {
+              uint2 u;
+              u.x = pack_bf16x2(o.x, o.y);
+              u.y = pack_bf16x2(o.z, o.w);
+              *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + ocol0 + c4g) = u;
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty[as]);
+        continue;
+      }
       const int nchunks = (outw + 31) / 32;
 #pragma unroll 1
       for (int c = cpar; c < nchunks; c += (NEW / 4)) {
