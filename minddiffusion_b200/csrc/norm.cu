@@ -2,10 +2,15 @@
 // See include/mdx.h (mdx_groupnorm, mdx_layernorm) for the reference call sites.
 //
 // GroupNorm = two passes over the activation (the minimum without a persistent cooperative kernel):
-//   gn_stats_kernel : each thread owns one 16-byte channel vector and walks pixel rows; per-channel fp32
-//                     partial sums -> per-group smem bins -> fp64 atomics into stats[n][group][{sum,sumsq}]
+//   gn_stats_kernel : each thread owns 8 consecutive channels and walks pixel rows (4 loads in flight); per-channel
+//                     fp32 partial sums -> per-group fp64 smem bins -> fp64 atomics into stats[n][group][{sum,sumsq}]
 //   gn_apply_kernel : y = x * a_c + b_c (a,b folded from mean/rstd/gamma/beta), optional SiLU, store.
 // Both take two sources so the UNet skip concat (openaimodel.py:566-571) is normalised without a copy.
+// Thread mapping: a 1-D block of CV*RP threads, CV = C/8 channel vectors x RP row lanes — no padding lanes, so a
+// 320-channel row (40 vectors) keeps every thread busy.
+//
+// LayerNorm: one warp handles R rows at a time, rows held in registers (NV float4 per lane per row), gamma/beta
+// loaded once per warp iteration; two-pass mean / variance in fp32.
 #include "common.cuh"
 #include "../../include/mdx.h"
 #include <atomic>
@@ -50,6 +55,7 @@ struct GnP {
   const void* x1; long long ld1; int C1;
   const void* x2; long long ld2; int C2;
   int n, HW, groups, cpg;
+  int CV, RP;             // channel vectors per row, row lanes per block
   int rows_per_block;
   float eps;
   const float* gamma; const float* beta;
@@ -59,162 +65,243 @@ struct GnP {
   double* stats;
 };
 
-// blockDim = (CVr, RP): x = channel-vector index, y = row lane
 template <typename T>
-__global__ void gn_stats_kernel(const GnP p) {
-  constexpr int V = Vec<T>::N;
-  __shared__ double bins[64][2];  // fp64 so that the (unordered) atomics cannot change the rounded result
-  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y) (&bins[0][0])[i] = 0.0;
-  __syncthreads();
-  const int C = p.C1 + p.C2;
-  const int c0 = threadIdx.x * V;
+__device__ __forceinline__ const T* gn_src(const GnP& p, int c0, int img, long long* ld) {
+  if (c0 < p.C1) {
+    *ld = p.ld1;
+    return reinterpret_cast<const T*>(p.x1) + (long long)img * p.HW * p.ld1 + c0;
+  }
+  *ld = p.ld2;
+  return reinterpret_cast<const T*>(p.x2) + (long long)img * p.HW * p.ld2 + (c0 - p.C1);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) gn_stats_kernel(const GnP p) {
+  constexpr int V = 8;
+  // per-thread partials for the (at most two) groups its 8 channels touch: {sum_lo, sq_lo, sum_hi, sq_hi}.
+  // Requires cpg >= 4 so that 8 channels span <= 3 groups... (cpg >= 8 -> <= 2 groups; smaller cpg handled below)
+  __shared__ float4 part[512];
+  __shared__ double bins[64][2];
+  const int cv = threadIdx.x % p.CV, rl = threadIdx.x / p.CV;
+  const int c0 = cv * V;
   const int img = blockIdx.y;
-  if (c0 < C) {
-    const T* src;
-    long long ld;
-    int cc;
-    if (c0 < p.C1) { src = reinterpret_cast<const T*>(p.x1); ld = p.ld1; cc = c0; }
-    else { src = reinterpret_cast<const T*>(p.x2); ld = p.ld2; cc = c0 - p.C1; }
-    const int r0 = blockIdx.x * p.rows_per_block;
-    const int r1 = min(p.HW, r0 + p.rows_per_block);
-    float s[V], ss[V];
+  long long ld;
+  const T* base = gn_src<T>(p, c0, img, &ld);
+  const int r0 = blockIdx.x * p.rows_per_block;
+  const int r1 = min(p.HW, r0 + p.rows_per_block);
+  const int RP = p.RP;
+  float s[V], ss[V];
 #pragma unroll
-    for (int i = 0; i < V; ++i) { s[i] = 0.f; ss[i] = 0.f; }
-    const T* base = src + (long long)img * p.HW * ld + cc;
-    for (int r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-      float v[V];
-      Vec<T>::load(base + (long long)r * ld, v);
+  for (int i = 0; i < V; ++i) { s[i] = 0.f; ss[i] = 0.f; }
+  int r = r0 + rl;
+  for (; r + 3 * RP < r1; r += 4 * RP) {
+    float v[4][V];
 #pragma unroll
-      for (int i = 0; i < V; ++i) { s[i] += v[i]; ss[i] = fmaf(v[i], v[i], ss[i]); }
-    }
+    for (int u = 0; u < 4; ++u) Vec<T>::load(base + (long long)(r + u * RP) * ld, v[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int i = 0; i < V; ++i) { s[i] += v[u][i]; ss[i] = fmaf(v[u][i], v[u][i], ss[i]); }
+  }
+  for (; r < r1; r += RP) {
+    float v[V];
+    Vec<T>::load(base + (long long)r * ld, v);
+#pragma unroll
+    for (int i = 0; i < V; ++i) { s[i] += v[i]; ss[i] = fmaf(v[i], v[i], ss[i]); }
+  }
+  if (p.cpg >= 8) {
+    // deterministic block reduction, no atomics: 8 channels touch at most two groups
+    const int g_lo = c0 / p.cpg;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < V; ++i) {
-      const int g = (c0 + i) / p.cpg;
-      atomicAdd(&bins[g][0], (double)s[i]);
-      atomicAdd(&bins[g][1], (double)ss[i]);
+      if ((c0 + i) / p.cpg == g_lo) { acc.x += s[i]; acc.y += ss[i]; }
+      else { acc.z += s[i]; acc.w += ss[i]; }
     }
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int g = threadIdx.x; g < p.groups; g += blockDim.x) {
+      const int cv_first = (g * p.cpg) / V, cv_last = (g * p.cpg + p.cpg - 1) / V;
+      double ds = 0.0, dq = 0.0;
+      for (int c = cv_first; c <= cv_last; ++c) {
+        const int glo = (c * V) / p.cpg;
+        for (int l = 0; l < RP; ++l) {
+          const float4 q = part[l * p.CV + c];
+          if (glo == g) { ds += q.x; dq += q.y; }
+          else if (glo + 1 == g) { ds += q.z; dq += q.w; }
+        }
+      }
+      atomicAdd(&p.stats[((long long)img * p.groups + g) * 2], ds);
+      atomicAdd(&p.stats[((long long)img * p.groups + g) * 2 + 1], dq);
+    }
+    return;
+  }
+  // narrow groups (cpg < 8, e.g. 192 channels): fp64 smem bins with atomics
+  for (int i = threadIdx.x; i < p.groups * 2; i += blockDim.x) (&bins[0][0])[i] = 0.0;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int g = (c0 + i) / p.cpg;
+    atomicAdd(&bins[g][0], (double)s[i]);
+    atomicAdd(&bins[g][1], (double)ss[i]);
   }
   __syncthreads();
-  for (int i = tid; i < p.groups * 2; i += blockDim.x * blockDim.y)
+  for (int i = threadIdx.x; i < p.groups * 2; i += blockDim.x)
     atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (&bins[0][0])[i]);
 }
 
 template <typename T, typename TO>
-__global__ void gn_apply_kernel(const GnP p) {
-  constexpr int V = Vec<T>::N;
-  const int C = p.C1 + p.C2;
-  const int c0 = threadIdx.x * V;
+__global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
+  constexpr int V = 8;
+  const int cv = threadIdx.x % p.CV, rl = threadIdx.x / p.CV;
+  const int c0 = cv * V;
   const int img = blockIdx.y;
-  if (c0 >= C) return;
-  const T* src;
   long long ld;
-  int cc;
-  if (c0 < p.C1) { src = reinterpret_cast<const T*>(p.x1); ld = p.ld1; cc = c0; }
-  else { src = reinterpret_cast<const T*>(p.x2); ld = p.ld2; cc = c0 - p.C1; }
+  const T* base = gn_src<T>(p, c0, img, &ld);
   float a[V], b[V];
   const double cnt = (double)p.HW * p.cpg;
+  // mean / rstd once per distinct group of this thread's channels (fp64 only for E[x^2] - mean^2)
+  int g_prev = -1;
+  float mean_f = 0.f, rstd_f = 0.f;
+  const double inv_cnt = 1.0 / cnt;
 #pragma unroll
   for (int i = 0; i < V; ++i) {
     const int c = c0 + i;
     const int g = c / p.cpg;
-    const double sum = p.stats[((long long)img * p.groups + g) * 2];
-    const double sq = p.stats[((long long)img * p.groups + g) * 2 + 1];
-    const double mean = sum / cnt;
-    double var = sq / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
-    a[i] = rstd * p.gamma[c];
-    b[i] = p.beta[c] - (float)mean * a[i];
+    if (g != g_prev) {
+      g_prev = g;
+      const double mean = p.stats[((long long)img * p.groups + g) * 2] * inv_cnt;
+      double var = p.stats[((long long)img * p.groups + g) * 2 + 1] * inv_cnt - mean * mean;
+      if (var < 0.0) var = 0.0;
+      mean_f = (float)mean;
+      rstd_f = rsqrtf((float)var + p.eps);
+    }
+    a[i] = rstd_f * __ldg(p.gamma + c);
+    b[i] = __ldg(p.beta + c) - mean_f * a[i];
   }
   const int r0 = blockIdx.x * p.rows_per_block;
   const int r1 = min(p.HW, r0 + p.rows_per_block);
-  const T* base = src + (long long)img * p.HW * ld + cc;
+  const int RP = p.RP;
   TO* obase = reinterpret_cast<TO*>(p.out) + (long long)img * p.HW * p.ldo + c0;
   TO* rbase = p.raw ? reinterpret_cast<TO*>(p.raw) + (long long)img * p.HW * p.ldraw + c0 : nullptr;
-  for (int r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-    float v[V];
-    Vec<T>::load(base + (long long)r * ld, v);
-    if (rbase) Vec<TO>::store(rbase + (long long)r * p.ldraw, v);
+  auto finish = [&](int row, float (&v)[V]) {
+    if (rbase) Vec<TO>::store(rbase + (long long)row * p.ldraw, v);
 #pragma unroll
     for (int i = 0; i < V; ++i) {
-      float y = fmaf(v[i], a[i], b[i]);
+      const float y = fmaf(v[i], a[i], b[i]);
       v[i] = p.silu ? silu_f(y) : y;
     }
-    Vec<TO>::store(obase + (long long)r * p.ldo, v);
+    Vec<TO>::store(obase + (long long)row * p.ldo, v);
+  };
+  int r = r0 + rl;
+  for (; r + 3 * RP < r1; r += 4 * RP) {
+    float v[4][V];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) Vec<T>::load(base + (long long)(r + u * RP) * ld, v[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) finish(r + u * RP, v[u]);
+  }
+  for (; r < r1; r += RP) {
+    float v[V];
+    Vec<T>::load(base + (long long)r * ld, v);
+    finish(r, v);
   }
 }
 
-// ---------------- LayerNorm: one warp per row, values held in registers ----------------
-template <typename T, typename TO, int MAXV>
+// ---------------- LayerNorm: one warp per R rows, rows held in registers ----------------
+template <typename T> __device__ __forceinline__ float4 ln_ld4(const T* p);
+template <> __device__ __forceinline__ float4 ln_ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 ln_ld4<bf16>(const bf16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+template <typename T> __device__ __forceinline__ void ln_st4(T* p, float4 v);
+template <> __device__ __forceinline__ void ln_st4<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <> __device__ __forceinline__ void ln_st4<bf16>(bf16* p, float4 v) {
+  uint2 u;
+  u.x = pack_bf16x2(v.x, v.y);
+  u.y = pack_bf16x2(v.z, v.w);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+template <typename T, typename TO, int NV, int R>
 __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, long long ldx, int rows, int C,
                                                         float eps, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, TO* __restrict__ out,
                                                         long long ldo) {
-  constexpr int V = Vec<T>::N;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (warp >= rows) return;
-  const int nvec = C / V;
-  const T* xr = x + (long long)warp * ldx;
-  float v[MAXV][V];
-  float s = 0.f;
+  const long long row0 = (long long)warp * R;
+  if (row0 >= rows) return;
+  const int nvec = C >> 2;
+  float4 v[R][NV];
 #pragma unroll
-  for (int j = 0; j < MAXV; ++j) {
-    const int vi = lane + j * 32;
-    if (vi < nvec) {
-      Vec<T>::load(xr + vi * V, v[j]);
+  for (int r = 0; r < R; ++r) {
+    const bool rok = row0 + r < rows;
+    const T* xr = x + (row0 + r) * ldx;
 #pragma unroll
-      for (int i = 0; i < V; ++i) s += v[j][i];
+    for (int j = 0; j < NV; ++j) {
+      const int vi = lane + j * 32;
+      v[r][j] = (rok && vi < nvec) ? ln_ld4<T>(xr + vi * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
-  s = warp_sum(s);
-  const float mean = s / (float)C;
-  float q = 0.f;
+  float mean[R], rstd[R];
 #pragma unroll
-  for (int j = 0; j < MAXV; ++j) {
-    const int vi = lane + j * 32;
-    if (vi < nvec) {
+  for (int r = 0; r < R; ++r) {
+    float s = 0.f;
 #pragma unroll
-      for (int i = 0; i < V; ++i) { float d = v[j][i] - mean; q = fmaf(d, d, q); }
-    }
+    for (int j = 0; j < NV; ++j) s += (v[r][j].x + v[r][j].y) + (v[r][j].z + v[r][j].w);
+    mean[r] = warp_sum(s) / (float)C;
   }
-  q = warp_sum(q);
-  const float rstd = rsqrtf(q / (float)C + eps);
-  TO* orow = out + (long long)warp * ldo;
 #pragma unroll
-  for (int j = 0; j < MAXV; ++j) {
-    const int vi = lane + j * 32;
-    if (vi < nvec) {
-      float y[V];
+  for (int r = 0; r < R; ++r) {
+    float q = 0.f;
 #pragma unroll
-      for (int i = 0; i < V; ++i) {
-        const int c = vi * V + i;
-        y[i] = (v[j][i] - mean) * rstd * gamma[c] + beta[c];
+    for (int j = 0; j < NV; ++j) {
+      if (lane + j * 32 < nvec) {
+        const float dx = v[r][j].x - mean[r], dy = v[r][j].y - mean[r], dz = v[r][j].z - mean[r], dw = v[r][j].w - mean[r];
+        q += (dx * dx + dy * dy) + (dz * dz + dw * dw);
       }
-      Vec<TO>::store(orow + vi * V, y);
+    }
+    rstd[r] = rsqrtf(warp_sum(q) / (float)C + eps);
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int vi = lane + j * 32;
+    if (vi < nvec) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + vi * 4));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(beta + vi * 4));
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        if (row0 + r < rows) {
+          float4 y;
+          y.x = (v[r][j].x - mean[r]) * rstd[r] * g.x + b.x;
+          y.y = (v[r][j].y - mean[r]) * rstd[r] * g.y + b.y;
+          y.z = (v[r][j].z - mean[r]) * rstd[r] * g.z + b.z;
+          y.w = (v[r][j].w - mean[r]) * rstd[r] * g.w + b.w;
+          ln_st4<TO>(out + (row0 + r) * ldo + vi * 4, y);
+        }
+      }
     }
   }
 }
 
 template <typename T, typename TO>
 int launch_gn(GnP p, cudaStream_t st) {
-  constexpr int V = Vec<T>::N;
   const int C = p.C1 + p.C2;
-  const int CV = C / V;
-  const int CVr = ((CV + 31) / 32) * 32;
-  MDX_CHECK_ARG(CVr <= 1024, "mdx_groupnorm: too many channels (%d)", C);
-  int RP = 512 / CVr;
-  if (RP < 1) RP = 1;
-  if (RP > 16) RP = 16;
-  // enough blocks to fill the machine, but at least 4*RP rows each
-  int chunks = (p.HW + 4 * RP - 1) / (4 * RP);
-  int want = (4 * 148 + p.n - 1) / p.n;
+  p.CV = C / 8;
+  MDX_CHECK_ARG(p.CV <= 512, "mdx_groupnorm: too many channels (%d)", C);
+  p.RP = 512 / p.CV;
+  if (p.RP > 16) p.RP = 16;
+  // about two waves of blocks, each at least 8*RP rows (4-deep unrolled loads twice)
+  int chunks = (p.HW + 8 * p.RP - 1) / (8 * p.RP);
+  int want = (8 * 148 + p.n - 1) / p.n;
   if (chunks > want) chunks = want;
   if (chunks < 1) chunks = 1;
   p.rows_per_block = (p.HW + chunks - 1) / chunks;
   chunks = (p.HW + p.rows_per_block - 1) / p.rows_per_block;
-  dim3 grid(chunks, p.n), block(CVr, RP);
+  dim3 grid(chunks, p.n), block(p.CV * p.RP);
   MDX_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, sizeof(double) * 2 * p.groups * p.n, st));
   gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
   MDX_CHECK_LAUNCH();
@@ -224,7 +311,37 @@ int launch_gn(GnP p, cudaStream_t st) {
   return MDX_OK;
 }
 
+template <typename T, typename TO, int NV, int R>
+void launch_ln_one(const void* x, long long ldx, int rows, int C, float eps, const float* gamma, const float* beta,
+                   void* out, long long ldo, cudaStream_t st) {
+  const int wpb = 8;
+  const long long warps = ((long long)rows + R - 1) / R;
+  dim3 grid((unsigned)((warps + wpb - 1) / wpb)), block(wpb * 32);
+  layernorm_kernel<T, TO, NV, R><<<grid, block, 0, st>>>((const T*)x, ldx, rows, C, eps, gamma, beta, (TO*)out, ldo);
+}
+
+template <typename T, typename TO>
+int launch_ln(const void* x, long long ldx, int rows, int C, float eps, const float* gamma, const float* beta,
+              void* out, long long ldo, cudaStream_t st) {
+  const int need = (C / 4 + 31) / 32;  // float4 vectors per lane
+  if (need <= 1) launch_ln_one<T, TO, 1, 4>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 2) launch_ln_one<T, TO, 2, 4>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 3) launch_ln_one<T, TO, 3, 4>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 5) launch_ln_one<T, TO, 5, 2>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 8) launch_ln_one<T, TO, 8, 1>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 10) launch_ln_one<T, TO, 10, 1>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else if (need <= 16) launch_ln_one<T, TO, 16, 1>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  else {
+    mdx_set_error("mdx_layernorm: C=%d too large (max 2048)", C);
+    return MDX_ERR_INVALID;
+  }
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}
+
 }  // namespace
+
 
 extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
                              int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma,
@@ -264,20 +381,13 @@ extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C
                 "mdx_layernorm: bad dtype");
   MDX_CHECK_ARG(!(in_dtype == MDX_BF16 && out_dtype == MDX_F32), "mdx_layernorm: bf16 -> fp32 is not supported");
   MDX_CHECK_ARG(C % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0, "mdx_layernorm: C and strides must be multiples of 8");
-  MDX_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0, "mdx_layernorm: 16-byte alignment");
-  MDX_CHECK_ARG(C / 8 <= 8 * 32, "mdx_layernorm: C=%d too large (max 2048)", C);
+  MDX_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)gamma & 15) == 0 &&
+                    ((uintptr_t)beta & 15) == 0,
+                "mdx_layernorm: 16-byte alignment");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const int wpb = 8;
-  dim3 grid((rows + wpb - 1) / wpb), block(wpb * 32);
-  if (in_dtype == MDX_BF16)
-    layernorm_kernel<bf16, bf16, 8><<<grid, block, 0, st>>>((const bf16*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
-  else if (out_dtype == MDX_BF16)
-    layernorm_kernel<float, bf16, 8><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (bf16*)out, ldo);
-  else
-    layernorm_kernel<float, float, 8><<<grid, block, 0, st>>>((const float*)x, ldx, rows, C, eps, gamma, beta, (float*)out, ldo);
-  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
-  MDX_CHECK_LAUNCH();
-  return MDX_OK;
+  if (in_dtype == MDX_BF16) return launch_ln<bf16, bf16>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  if (out_dtype == MDX_BF16) return launch_ln<float, bf16>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
+  return launch_ln<float, float>(x, ldx, rows, C, eps, gamma, beta, out, ldo, st);
 }
 
 // ---------------------------------------------------------------------------------------------------------
