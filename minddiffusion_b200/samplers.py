@@ -275,7 +275,7 @@ class DPMSolverSampler(object):
         t_0, t_T = 1. / ns.total_N, ns.T
         # get_time_steps('time_uniform'): fp32 linspace cast to fp16 (dpm_solver.py:414-415)
         timesteps = np.linspace(np.float32(t_T), np.float32(t_0), steps + 1, dtype=np.float32).astype(np.float16)
-        x = img
+        x = img.to(torch.float16).to(torch.float32)  # ops.Cast()(img, ms.float16), sampler.py:89
         x0_prev = None
         for i in range(steps):
             s16 = timesteps[i]

@@ -14,8 +14,8 @@ Pinning: see oracle/sd_unet.py; the same golden-vector script runs the unmodifie
 
 Precision notes: the reference stores the schedule in the model dtype and, in the DPM-Solver path,
 rounds the time grid and `t_array` to fp16 unconditionally (dpm_solver.py:100-103,415) and computes the model
-input time in fp16 (dpm_solver.py:256-265 on an fp16 tensor).  Those fp16 roundings are reproduced; tensor state
-(x, eps, x0) is kept in fp32 (the reference casts x to fp16 at sampler.py:89 — deliberately not followed).
+input time in fp16 (dpm_solver.py:256-265 on an fp16 tensor), and rounds x_T to fp16 once (sampler.py:89; the state
+is promoted back to fp32 by the first update because eps and the coefficients are fp32).  All of these are reproduced.
 """
 import numpy as np
 import torch
@@ -195,7 +195,7 @@ def dpmpp2m_sample(model_fn, sched, S, x_T, cond, uncond=None, scale=1.0, model_
     ns = NoiseScheduleVP(sched["alphas_cumprod"])
     t_0 = 1.0 / ns.total_N
     timesteps = dpm_time_steps(S, ns.T, t_0)
-    x = x_T.clone()
+    x = x_T.to(torch.float16).to(torch.float32)  # ops.Cast()(img, ms.float16), sampler.py:89 (state is fp32 afterwards)
     b = x.shape[0]
 
     def model_eval(x, t16):  # model_wrapper.model_fn + data_prediction_fn, dpm_solver.py:302-325,366-373

@@ -148,7 +148,8 @@ def test_oracle_samplers_closed_form():
         h = ns.marginal_lambda(b)[0] - ns.marginal_lambda(a)[0]
         return float(ns.marginal_std(b)[0] / ns.marginal_std(a)[0]) * xv - \
             float(ns.marginal_alpha(b)[0] * np.expm1(-h)) * (xv / float(ns.marginal_alpha(a)[0]))
-    want = step1(step1(x, s, t1), t1, t2)  # S=2 < 15: the last step falls back to order 1
+    x16 = x.to(torch.float16).to(torch.float32)  # the reference rounds x_T to fp16 once (sampler.py:89)
+    want = step1(step1(x16, s, t1), t1, t2)  # S=2 < 15: the last step falls back to order 1
     assert torch.allclose(got, want, rtol=1e-4, atol=1e-5)
     assert float(osamp.dpm_model_input_time(np.float16(1.0))) == 999.0  # fp16 rounding of (1 - 1/1000) * 1000
 

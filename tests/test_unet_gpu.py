@@ -201,3 +201,38 @@ def test_sd2_config1_two_step_plms_bf16():
     got, _ = samplers.PLMSSampler(ldm).sample(2, 1, (4, 32, 32), c.cuda(), x_T=x_T.cuda(), verbose=False,
                                               unconditional_guidance_scale=7.5, unconditional_conditioning=uc.cuda())
     assert cosine(got, ref) >= 0.999
+
+
+@pytest.mark.parametrize("family,cfg", [("sd2", TINY_UNET), ("wukong", TINY_UNET_V1)])
+def test_cuda_path_against_executed_reference_goldens(family, cfg):
+    """The CUDA path against tests/golden/*.npz — outputs of the UNMODIFIED reference sources executed by
+    tests/golden/make_golden.py (UNet evaluation, 6-step guided PLMS, 6- and 20-step guided DPM-Solver++)."""
+    import os
+    from conftest import ROOT
+    from minddiffusion_b200 import samplers
+    G = dict(np.load(os.path.join(ROOT, "tests", "golden", "%s_golden.npz" % family)))
+    rs = np.random.RandomState(1)
+    x = torch.from_numpy(rs.randn(2, 4, 16, 16).astype(np.float32))
+    ctx = torch.from_numpy(rs.randn(2, 77, cfg["context_dim"]).astype(np.float32))
+    t = torch.tensor([981.0, 21.0])
+    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 1.25e-2)):
+        model, _ = build(cfg, dtype, seed=0)
+        model.set_context(ctx.cuda())
+        eps = model.forward_nhwc(x.cuda(), t.cuda())[..., :4].permute(0, 3, 1, 2)
+        assert rel_err(eps, torch.from_numpy(G["unet_eps"])) < tol
+        rs2 = np.random.RandomState(42)
+        x_T = torch.from_numpy(rs2.randn(2, 4, 16, 16).astype(np.float32)).cuda()
+        c = torch.from_numpy(rs2.randn(2, 77, cfg["context_dim"]).astype(np.float32)).cuda()
+        uc = torch.from_numpy(np.random.RandomState(44).randn(2, 77, cfg["context_dim"]).astype(np.float32)).cuda()
+        ldm = _ldm(model)
+        kw = dict(x_T=x_T, verbose=False, unconditional_guidance_scale=7.5, unconditional_conditioning=uc)
+        out, inter = samplers.PLMSSampler(ldm).sample(6, 2, (4, 16, 16), c, **kw)
+        assert len(inter["x_inter"]) == int(G["plms_n_inter"])
+        d6, _ = samplers.DPMSolverSampler(ldm).sample(6, 2, (4, 16, 16), c, **kw)
+        d20, _ = samplers.DPMSolverSampler(ldm).sample(20, 2, (4, 16, 16), c, **kw)
+        for got, key in ((out, "plms_out"), (d6, "dpm_out_6"), (d20, "dpm_out_20")):
+            ref = torch.from_numpy(G[key])
+            assert cosine(got, ref) >= 0.999, key
+            if dtype == torch.float32:
+                assert rel_err(got, ref) < 2e-3, key
+        del model
