@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--latent", type=int, default=64)
     ap.add_argument("--scale", type=float, default=7.5)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--cfg-split", action="store_true",
+                    help="N >= 2: split the cond/uncond halves of each batch across GPU pairs (per-step eps exchange)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -187,12 +189,20 @@ def run_b200(a):
     del P
     unet.use_cuda_graph = not a.no_graph
     ldm = LatentDiffusion(unet, timesteps=1000, linear_start=0.00085, linear_end=0.012, scale_factor=0.18215)
+    groups = world  # independent prompt batches in flight
+    seed_id = rank
+    if a.cfg_split:
+        if world < 2 or world % 2:
+            raise SystemExit("--cfg-split needs an even number of GPUs")
+        from minddiffusion_b200.parallel import CfgPairSplit
+        ldm.cfg_split = CfgPairSplit()
+        groups, seed_id = world // 2, rank // 2  # both ranks of a pair work on the same prompt batch
     sampler = samplers.DDIMSampler(ldm)
 
     B, S, h = a.batch, a.sampler_steps, a.latent
     shape = (4, h, h)
     # synthetic inputs of the reference shapes: x_T seed 42 (+rank), c / uc seeds 43 / 44
-    x_host = torch.from_numpy(np.random.RandomState(42 + rank).randn(B, *shape).astype(np.float32)).pin_memory()
+    x_host = torch.from_numpy(np.random.RandomState(42 + seed_id).randn(B, *shape).astype(np.float32)).pin_memory()
     c_host = torch.from_numpy(np.random.RandomState(43).randn(B, 77, 1024).astype(np.float32)).pin_memory()
     uc_host = torch.from_numpy(np.random.RandomState(44).randn(B, 77, 1024).astype(np.float32)).pin_memory()
     out_host = torch.empty((B, *shape), dtype=torch.float32).pin_memory()
@@ -242,7 +252,7 @@ def run_b200(a):
     ms_e2e = timed(step_e2e, a.steps)
     clk = clocks.stop() if rank == 0 else None
 
-    images = B * world * a.steps
+    images = B * groups * a.steps
     value = images / (ms / 1e3)
     e2e = images / (ms_e2e / 1e3)
 
@@ -250,8 +260,9 @@ def run_b200(a):
     prof = []
     ops.GEMM_TC_PROFILE = prof
     unet.use_cuda_graph = False
-    t_probe = torch.full((2 * B,), 501.0, device=dev)
-    unet.forward_nhwc(x_dev, t_probe, repeat=2)
+    rep = 1 if a.cfg_split else 2
+    t_probe = torch.full((rep * B,), 501.0, device=dev)
+    unet.forward_nhwc(x_dev, t_probe, repeat=rep)
     torch.cuda.synchronize()
     ops.GEMM_TC_PROFILE = None
     flops = sum(p_[0] for p_ in prof)
@@ -265,7 +276,7 @@ def run_b200(a):
     peak_kind = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md, sustained)"
     achieved = flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
     fwd_flops = FLOP_PER_SAMPLE_FWD_SD2_64 * (h / 64.0) ** 2  # conv/linear scale ~ pixels; attention differs slightly
-    step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None
+    step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None  # per GPU
 
     if rank != 0:
         if world > 1:
@@ -283,8 +294,9 @@ def run_b200(a):
         "metric": "images/sec @512^2 50-step DDIM CFG7.5", "value": value, "unit": "images/s", "n_gpus": world,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": workload_name(a), "global_batch": B * world, "sampler": "DDIM", "sampler_steps": S,
-                   "cfg_scale": a.scale, "parallelism": "dp%d (independent prompt batches, no collective)" % world,
+        "config": {"workload": workload_name(a), "global_batch": B * groups, "sampler": "DDIM", "sampler_steps": S,
+                   "cfg_scale": a.scale, "parallelism": ("dp%d x cfg-pair-split (per-step 2-rank eps all-gather over NCCL)" % groups) if a.cfg_split
+                   else "dp%d (independent prompt batches, no collective)" % world,
                    "l2": "inputs larger than L2 (weights 1.7 GB + activations >> 126 MB)",
                    "cuda_graph": not a.no_graph},
         "clocks": clk,

@@ -75,10 +75,18 @@ class _GuidedUNet:
         self.scale = float(scale)
         if isinstance(cond, dict):
             raise NotImplementedError("dict conditioning (hybrid / inpaint) is outside this path's scope")
-        ctx = torch.cat((uncond, cond), dim=0) if self.cfg else cond  # order of plms.py:194
+        # optional: the two halves of the guided batch on two GPUs (minddiffusion_b200.parallel.CfgPairSplit)
+        self.split = getattr(model, "cfg_split", None) if self.cfg else None
+        if self.split is not None:
+            ctx = self.split.my_context(cond, uncond)
+        else:
+            ctx = torch.cat((uncond, cond), dim=0) if self.cfg else cond  # order of plms.py:194
         self.unet.set_context(ctx)
 
     def __call__(self, x, t_value):
+        if self.split is not None:
+            t = torch.full((x.shape[0],), float(t_value), dtype=torch.float32, device=x.device)
+            return self.split.exchange(self.unet.forward_nhwc(x, t, repeat=1))  # [uncond half | cond half]
         n = x.shape[0] * (2 if self.cfg else 1)
         t = torch.full((n,), float(t_value), dtype=torch.float32, device=x.device)
         return self.unet.forward_nhwc(x, t, repeat=2 if self.cfg else 1)
