@@ -61,6 +61,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ float max3f(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -123,6 +128,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   const uint32_t TM_S = tmem_base;          // S[sb] at columns sb*128
   const uint32_t TM_O = tmem_base + 256;    // O[ob] at columns 256 + ob*64
 
+  // Register rebalancing: the producer / MMA / allocator warpgroup needs few registers, the softmax warpgroups hold a
+  // whole score row (128) plus the running output row (64) each.  384 threads x 168 = 128 x 40 + 256 x 232.
+  // (setmaxnreg is issued at the top of each warpgroup's own branch so that ptxas can size the two regions.)
+
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
   if (warp == 0) {
     if (elect_one()) {
       // ===================== TMA producer =====================
@@ -179,7 +191,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       }
       issue_pv(T - 1);
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     // ===================== softmax + output =====================
     // Two warpgroups ping-pong over the key tiles: group g owns tiles j = g, g+2, ... and with them S[g], P[g],
     // O[g].  Each keeps its own running (max, sum, O) — two independent online-softmax streams — merged once at
@@ -203,62 +217,45 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mbar_wait(&s_full[g], it & 1);
       tc_fence_after();
       const int key0 = j * AT_BN;
-      // ---- pass 1: row max (four independent chains: one warp per scheduler cannot hide a 32-deep one) ----
+      // ---- one pass over S: all 128 scores of the row into registers (4 TMEM loads in flight, one wait) ----
+      uint32_t sr[AT_BN];
+#pragma unroll
+      for (int cc = 0; cc < AT_BN / 32; ++cc) tmem_ld32(ts + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
+      tmem_ld_wait();
+      if (key0 + AT_BN > p.Nk) {  // ragged last tile: keys beyond Nk count as -inf
+#pragma unroll
+        for (int i = 0; i < AT_BN; ++i)
+          if (key0 + i >= p.Nk) sr[i] = 0xff800000u;
+      }
+      // row max: 3-input max (FMNMX3), four independent chains
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-#pragma unroll 1
-      for (int cc = 0; cc < AT_BN / 32; ++cc) {
-        uint32_t r[32];
-        tmem_ld32(ts + cc * 32, r);
-        tmem_ld_wait();
-        const int kb = key0 + cc * 32;
-        if (kb + 32 <= p.Nk) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            mx0 = fmaxf(mx0, __uint_as_float(r[i]));
-            mx1 = fmaxf(mx1, __uint_as_float(r[i + 1]));
-            mx2 = fmaxf(mx2, __uint_as_float(r[i + 2]));
-            mx3 = fmaxf(mx3, __uint_as_float(r[i + 3]));
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (kb + i < p.Nk) mx0 = fmaxf(mx0, __uint_as_float(r[i]));
-        }
+      for (int i = 0; i < AT_BN; i += 8) {
+        mx0 = max3f(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+        mx1 = max3f(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+        mx2 = max3f(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
+        mx3 = max3f(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
       }
       const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       const float m_new = fmaxf(m_run, mx);
       const float alpha = ex2_approx((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
       const float msc = m_new * c;
-      // ---- pass 2: p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
+      // ---- p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
       mbar_wait(&p_empty[g], (it & 1) ^ 1);
       float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-      for (int cc = 0; cc < AT_BN / 32; ++cc) {
-        uint32_t r[32];
-        tmem_ld32(ts + cc * 32, r);
-        tmem_ld_wait();
-        const int kb = key0 + cc * 32;
-        const bool full = kb + 32 <= p.Nk;
-        uint8_t* pblk = prow + (cc >> 1) * TILE_BYTES;       // K-block of 64 keys
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {                     // 4 chunks of 8 keys (16 B)
-          uint32_t pk[4];
+      for (int ch = 0; ch < AT_BN / 8; ++ch) {                // 16 chunks of 8 keys (16 B each)
+        uint32_t pk[4];
 #pragma unroll
-          for (int h = 0; h < 4; ++h) {
-            const int i = ch * 8 + h * 2;
-            float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-            if (!full) {
-              if (kb + i >= p.Nk) s0 = -INFINITY;
-              if (kb + i + 1 >= p.Nk) s1 = -INFINITY;
-            }
-            const float p0 = ex2_approx(fmaf(s0, c, -msc));
-            const float p1 = ex2_approx(fmaf(s1, c, -msc));
-            rs4[h] += p0 + p1;
-            pk[h] = pack_bf16x2(p0, p1);
-          }
-          const int chunk = (cc & 1) * 4 + ch;               // 16-byte chunk index inside the 128-byte row
-          *reinterpret_cast<uint4*>(pblk + ((chunk ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        for (int h = 0; h < 4; ++h) {
+          const int i = ch * 8 + h * 2;
+          const float p0 = ex2_approx(fmaf(__uint_as_float(sr[i]), c, -msc));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(sr[i + 1]), c, -msc));
+          rs4[h] += p0 + p1;
+          pk[h] = pack_bf16x2(p0, p1);
         }
+        uint8_t* pblk = prow + (ch >> 3) * TILE_BYTES;        // K-block of 64 keys
+        *reinterpret_cast<uint4*>(pblk + (((ch & 7) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
       l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
       m_run = m_new;
