@@ -70,6 +70,8 @@ typedef struct mdx_gemm_args {
   int32_t residual_dtype; /* MDX_BF16 or MDX_F32 (the fp32 residual trunk, see DESIGN.md "precision") */
   int32_t geglu;
   int32_t block_n;
+  int32_t act; /* applied after bias/rowbias, before the residual: 0 none, 1 GELU (tanh form, nn.GELU() of
+                  encoders/text_encoder.py:67-69), 2 QuickGELU x*sigmoid(1.702x) (wukong text_encoder.py:67-74) */
 } mdx_gemm_args;
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
 /* BLOCK_N the library would pick for a GEMM with N output columns (needed to pack GEGLU weights). */
@@ -101,6 +103,7 @@ typedef struct mdx_conv_args {
   int64_t ld_rowbias;
   const void* residual;
   int64_t ldr;
+  int32_t act; /* as mdx_gemm_args.act */
 } mdx_conv_args;
 int mdx_conv_direct(const mdx_conv_args* args, void* stream);
 
@@ -151,10 +154,23 @@ int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps
  *  q: [batch, Nq, heads*d] (row stride ldq), k/v: [batch, Nk, heads*d] (ldk/ldv), o: [batch, Nq, heads*d] (ldo).
  *  Batch strides are Nq*ldq etc. (tensors are dense over batch).  dtype MDX_BF16: flash kernel on mma.sync
  *  tensor cores with fp32 softmax; MDX_F32: CUDA-core check-mode kernel.  d <= 160, d % 8 == 0.
+ *  causal != 0: key j is visible to query i only if j <= i (the text tower's triu(-inf, 1) mask,
+ *  encoders/text_encoder.py:131-134); uses the mma.sync kernel for every head dim.
  * --------------------------------------------------------------------------------------------------------- */
 int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv, void* o,
                   int64_t ldo, int32_t batch, int32_t heads, int32_t Nq, int32_t Nk, int32_t d, float scale,
-                  int32_t dtype, void* stream);
+                  int32_t dtype, int32_t causal, void* stream);
+
+/* Row softmax out[r, :] = softmax(x[r, :] * scale) (fp32 math).  Used by the VAE decoder's single-head attention over
+ * 512 channels (diffusionmodules/model.py:190-204), whose head dim exceeds the flash kernels': the scores are
+ * materialised by mdx_gemm_tc, normalised here, and multiplied with V by mdx_gemm_tc.  in: fp32 or bf16, out: bf16/fp32. */
+int mdx_softmax_rows(const void* x, int64_t ldx, int64_t rows, int32_t cols, float scale, void* out, int64_t ldo,
+                     int32_t in_dtype, int32_t out_dtype, void* stream);
+
+/* Token embedding + positional embedding (encoders/text_encoder.py:143-148): out[i, :] = table[ids[i], :] + pos[i % L, :].
+ * table: fp32 [vocab, width], pos: fp32 [L, width], ids: int32 [n] (n = batch * L), out: [n, width] (dtype). */
+int mdx_embedding(const float* table, int32_t vocab, int32_t width, const float* pos, int32_t L, const int32_t* ids,
+                  int32_t n, void* out, int32_t dtype, void* stream);
 
 /* GEGLU product for check mode: out[m, j] = x[m, j] * gelu_tanh(x[m, I + j]) (attention.py:47-51). */
 int mdx_geglu(const void* x, int64_t ldx, int32_t rows, int32_t I, void* out, int64_t ldo, int32_t dtype,

@@ -39,6 +39,7 @@ class GemmArgs(ctypes.Structure):
         ("residual_dtype", c_int),
         ("geglu", c_int),
         ("block_n", c_int),
+        ("act", c_int),
     ]
 
 
@@ -52,6 +53,7 @@ class ConvArgs(ctypes.Structure):
         ("out", c_p), ("ldo", c_i64), ("out_dtype", c_int),
         ("bias", c_p), ("rowbias", c_p), ("ld_rowbias", c_i64),
         ("residual", c_p), ("ldr", c_i64),
+        ("act", c_int),
     ]
 
 
@@ -69,7 +71,9 @@ SIGNATURES = {
                                       c_p, c_i64, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_layernorm": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_p, c_p, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_attention": (c_int, [c_p, c_i64, c_p, c_i64, c_p, c_i64, c_p, c_i64, c_int, c_int, c_int, c_int, c_int, c_f,
-                              c_int, c_p]),
+                              c_int, c_int, c_p]),
+    "mdx_softmax_rows": (c_int, [c_p, c_i64, c_i64, c_int, c_f, c_p, c_i64, c_int, c_int, c_p]),
+    "mdx_embedding": (c_int, [c_p, c_int, c_int, c_p, c_int, c_p, c_int, c_p, c_int, c_p]),
     "mdx_geglu": (c_int, [c_p, c_i64, c_int, c_int, c_p, c_i64, c_int, c_p]),
     "mdx_timestep_embedding": (c_int, [c_p, c_int, c_int, c_f, c_p, c_p]),
     "mdx_nchw_to_nhwc": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_p, c_int, c_p]),

@@ -21,6 +21,7 @@ struct AttnP {
   void* o; long long ldo;
   int batch, heads, Nq, Nk, d;
   float scale;
+  int causal;
 };
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem) {
@@ -131,6 +132,13 @@ __global__ void __launch_bounds__(256, 1) flash_attn_bf16_kernel(const AttnP p) 
       const int key = kbase + j * 8 + 2 * t4;
       if (key >= p.Nk) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
       if (key + 1 >= p.Nk) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+      if (p.causal) {  // key j visible to query i only if j <= i
+        const int qr0 = q0 + warp * 16 + g, qr1 = qr0 + 8;
+        if (key > qr0) s[j][0] = -INFINITY;
+        if (key + 1 > qr0) s[j][1] = -INFINITY;
+        if (key > qr1) s[j][2] = -INFINITY;
+        if (key + 1 > qr1) s[j][3] = -INFINITY;
+      }
       mx[0] = fmaxf(mx[0], fmaxf(s[j][0], s[j][1]));
       mx[1] = fmaxf(mx[1], fmaxf(s[j][2], s[j][3]));
     }
@@ -223,7 +231,7 @@ __global__ void __launch_bounds__(128) attn_f32_kernel(const AttnP p) {
   for (int k0 = 0; k0 < p.Nk; k0 += 32) {
     const int key = k0 + lane;
     float s = -INFINITY;
-    if (key < p.Nk) {
+    if (key < p.Nk && !(p.causal && key > qi)) {
       const float* kr = gk + (long long)key * p.ldk;
       float dot = 0.f;
       for (int i = 0; i < d; ++i) dot = fmaf(sq[warp][i], kr[i], dot);
@@ -231,7 +239,7 @@ __global__ void __launch_bounds__(128) attn_f32_kernel(const AttnP p) {
     }
     const float m_new = fmaxf(m, warp_max(s));
     const float corr = __expf(m - m_new);
-    const float pe = key < p.Nk ? __expf(s - m_new) : 0.f;
+    const float pe = (key < p.Nk && !(p.causal && key > qi)) ? __expf(s - m_new) : 0.f;
     l = l * corr + warp_sum(pe);
     m = m_new;
     sp[warp][lane] = pe;
@@ -279,12 +287,12 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
 
 extern "C" int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                              void* o, int64_t ldo, int32_t batch, int32_t heads, int32_t Nq, int32_t Nk, int32_t d,
-                             float scale, int32_t dtype, void* stream) {
+                             float scale, int32_t dtype, int32_t causal, void* stream) {
   MDX_CHECK_ARG(q && k && v && o, "mdx_attention: NULL operand");
   MDX_CHECK_ARG(batch > 0 && heads > 0 && Nq > 0 && Nk > 0, "mdx_attention: empty problem");
   MDX_CHECK_ARG(d > 0 && d <= 160 && d % 8 == 0, "mdx_attention: head dim %d unsupported (need d %% 8 == 0, d <= 160)", d);
   MDX_CHECK_ARG(heads <= 65535 && batch <= 65535, "mdx_attention: too many heads/batches");
-  AttnP p{q, ldq, k, ldk, v, ldv, o, ldo, batch, heads, Nq, Nk, d, scale};
+  AttnP p{q, ldq, k, ldk, v, ldv, o, ldo, batch, heads, Nq, Nk, d, scale, causal};
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == MDX_F32) {
     dim3 grid((Nq + 3) / 4, heads, batch);
@@ -299,7 +307,7 @@ extern "C" int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t 
                 "mdx_attention: operands must be 16-byte aligned");
   // head dim 64 (every attention layer of the SD2 UNet): tcgen05/TMEM kernel; MDX_ATTN_LEGACY=1 keeps mma.sync
   static const bool legacy = getenv("MDX_ATTN_LEGACY") != nullptr;
-  if (d == 64 && !legacy && ldo % 8 == 0 && ((uintptr_t)o & 15) == 0)
+  if (d == 64 && !legacy && !causal && ldo % 8 == 0 && ((uintptr_t)o & 15) == 0)
     return mdx_attention_tc_d64(q, ldq, k, ldk, v, ldv, o, ldo, batch, heads, Nq, Nk, scale, st);
   if (d <= 48) return launch_fa<48>(p, st);
   if (d <= 64) return launch_fa<64>(p, st);

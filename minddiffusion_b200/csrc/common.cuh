@@ -70,6 +70,18 @@ __device__ __forceinline__ float gelu_tanh_fast(float x) {
   return x * r;
 }
 
+// epilogue activations: 1 = GELU (tanh form), 2 = QuickGELU x * sigmoid(1.702 x)
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == 1) return gelu_tanh_fast(x);
+  if (act == 2) return x / (1.f + __expf(-1.702f * x));
+  return x;
+}
+__device__ __forceinline__ float apply_act_precise(float x, int act) {
+  if (act == 1) return gelu_tanh_f(x);
+  if (act == 2) return x / (1.f + expf(-1.702f * x));
+  return x;
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

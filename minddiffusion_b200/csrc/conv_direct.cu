@@ -23,6 +23,7 @@ struct ConvP {
   void* out; long long ldo;
   const float* bias; const float* rowbias; long long ld_rowbias;
   const void* residual; long long ldr;
+  int act;
 };
 
 constexpr int TM = 64, TN = 64, TK = 16;
@@ -113,6 +114,7 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const ConvP p) {
       float v = acc[i][j];
       if (p.bias) v += p.bias[col];
       if (p.rowbias) v += p.rowbias[(long long)rimg * p.ld_rowbias + col];
+      if (p.act) v = apply_act_precise(v, p.act);
       if (res) v += to_f32<TO>(res[row * p.ldr + col]);
       out[row * p.ldo + col] = from_f32<TO>(v);
     }
@@ -138,7 +140,7 @@ extern "C" int mdx_conv_direct(const mdx_conv_args* a, void* stream) {
   p.M = (long long)a->n * p.OH * p.OW;
   p.K = a->kh * a->kw * a->Cin;
   p.out = a->out; p.ldo = a->ldo; p.bias = a->bias; p.rowbias = a->rowbias; p.ld_rowbias = a->ld_rowbias;
-  p.residual = a->residual; p.ldr = a->ldr;
+  p.residual = a->residual; p.ldr = a->ldr; p.act = a->act;
   long long gx = (p.M + TM - 1) / TM;
   MDX_CHECK_ARG(gx < (1ll << 31), "mdx_conv_direct: too many rows");
   dim3 grid((unsigned)gx, (unsigned)((a->Cout + TN - 1) / TN));

@@ -42,6 +42,7 @@ struct TcParams {
   long long ldr;
   int res_f32;
   int geglu;
+  int act;
 };
 
 template <int BN> struct TcCfg {
@@ -346,7 +347,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           const long long pix = pixs[pass];
           if (!col_ok || pix < 0) continue;
           float4 o = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + c4);
-          o.x += bz.x + radd[pass].x; o.y += bz.y + radd[pass].y; o.z += bz.z + radd[pass].z; o.w += bz.w + radd[pass].w;
+          if (p.act) {  // activation sits between the bias and the residual (radd carries rowbias + residual)
+            o.x = apply_act(o.x + bz.x, p.act) + radd[pass].x; o.y = apply_act(o.y + bz.y, p.act) + radd[pass].y;
+            o.z = apply_act(o.z + bz.z, p.act) + radd[pass].z; o.w = apply_act(o.w + bz.w, p.act) + radd[pass].w;
+          } else {
+            o.x += bz.x + radd[pass].x; o.y += bz.y + radd[pass].y; o.z += bz.z + radd[pass].z; o.w += bz.w + radd[pass].w;
+          }
           if (p.out_f32) {
             *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0 + c4) = o;
           } else {
@@ -522,7 +528,9 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   if (a->rowbias)
     MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->rowbias) & 15) == 0 && a->ld_rowbias % 4 == 0,
                   "mdx_gemm_tc: rowbias alignment");
-  if (a->geglu) MDX_CHECK_ARG(!a->rowbias && !a->residual && a->N % 32 == 0, "mdx_gemm_tc: geglu excludes rowbias/residual");
+  if (a->geglu) MDX_CHECK_ARG(!a->rowbias && !a->residual && !a->act && a->N % 32 == 0, "mdx_gemm_tc: geglu excludes rowbias/residual/act");
+  MDX_CHECK_ARG(a->act >= 0 && a->act <= 2, "mdx_gemm_tc: act must be 0, 1 (gelu) or 2 (quick gelu)");
+  if (a->act) MDX_CHECK_ARG(!a->rowbias, "mdx_gemm_tc: act excludes rowbias");
 
   TcParams p;
   memset(&p, 0, sizeof(p));
@@ -558,6 +566,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   p.bias = a->bias; p.rowbias = a->rowbias; p.ld_rowbias = a->ld_rowbias;
   p.residual = a->residual; p.ldr = a->ldr; p.res_f32 = a->residual_dtype == MDX_F32;
   p.geglu = a->geglu;
+  p.act = a->act;
 
   CUtensorMap maps[3];
   for (int s = 0; s < 3; ++s) {

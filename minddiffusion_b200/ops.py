@@ -59,8 +59,11 @@ def pick_block_n(N, geglu=False):
     return int(_lib.load().mdx_gemm_tc_pick_block_n(N, 1 if geglu else 0))
 
 
+ACT = {None: 0, "gelu": 1, "quick_gelu": 2}
+
+
 def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
-            block_n=0):
+            block_n=0, act=None):
     """Tensor-core implicit GEMM (mdx_gemm_tc).
 
     segs: list of (a, taps); a is bf16 ``[n, H, W, C]`` (conv view) or ``[M, C]`` (dense), taps 9 or 1.
@@ -118,6 +121,7 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
         args.residual_dtype = _dt(residual)
     args.geglu = 1 if geglu else 0
     args.block_n = block_n
+    args.act = ACT[act]
     if GEMM_TC_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -132,7 +136,7 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
 
 
 def conv_direct(x, w, kh=1, kw=1, stride=1, pad=0, upsample=False, pre_silu=False, bias=None, rowbias=None,
-                residual=None, out=None, out_dtype=None):
+                residual=None, out=None, out_dtype=None, act=None):
     """CUDA-core implicit-GEMM conv/dense (mdx_conv_direct). x: [n,H,W,Cin] or [M,Cin]; w: [Cout, kh*kw*Cin]."""
     lib = _lib.load()
     if x.dim() == 4:
@@ -169,6 +173,7 @@ def conv_direct(x, w, kh=1, kw=1, stride=1, pad=0, upsample=False, pre_silu=Fals
             raise TypeError("residual must have the out dtype")
         rr, rc, ldr = _rows_ld(residual)
         a.residual, a.ldr = residual.data_ptr(), ldr
+    a.act = ACT[act]
     check(lib.mdx_conv_direct(ctypes.byref(a), _stream()), "mdx_conv_direct")
     return out
 
@@ -215,7 +220,30 @@ def layernorm(x, gamma, beta, eps=1e-5, out=None, out_dtype=None):
     return out
 
 
-def attention(q, k, v, heads, scale, out=None):
+def softmax_rows(x, scale=1.0, out_dtype=None):
+    """Row softmax of a [rows, cols] view: softmax(x * scale) along the last dim (fp32 math)."""
+    lib = _lib.load()
+    rows, cols, ldx = _rows_ld(x)
+    out = torch.empty((rows, cols), dtype=out_dtype or x.dtype, device=x.device)
+    check(lib.mdx_softmax_rows(_p(x), ldx, rows, cols, float(scale), _p(out), cols, _dt(x), _dt(out), _stream()),
+          "mdx_softmax_rows")
+    return out
+
+
+def embedding(table, pos, ids, dtype=torch.float32):
+    """out[i] = table[ids[i]] + pos[i % L]; table/pos fp32, ids int32 [batch, L] -> [batch*L, width]."""
+    lib = _lib.load()
+    table, pos = _f32(table, "table"), _f32(pos, "pos")
+    if ids.dtype != torch.int32 or not ids.is_contiguous() or not ids.is_cuda:
+        raise TypeError("ids must be a contiguous int32 CUDA tensor")
+    n, L, width = ids.numel(), pos.shape[0], table.shape[1]
+    out = torch.empty((n, width), dtype=dtype, device=table.device)
+    check(lib.mdx_embedding(_p(table), table.shape[0], width, _p(pos), L, _p(ids), n, _p(out), _DT[dtype], _stream()),
+          "mdx_embedding")
+    return out
+
+
+def attention(q, k, v, heads, scale, out=None, causal=False):
     """q: [B, Nq, heads*d] view, k/v: [B, Nk, heads*d] views (dense over batch). Returns [B, Nq, heads*d]."""
     lib = _lib.load()
     B, Nq, HDm = q.shape
@@ -227,7 +255,7 @@ def attention(q, k, v, heads, scale, out=None):
     if out is None:
         out = torch.empty((B, Nq, HDm), dtype=q.dtype, device=q.device)
     check(lib.mdx_attention(_p(q), q.stride(1), _p(k), k.stride(1), _p(v), v.stride(1), _p(out), out.stride(1), B,
-                            heads, Nq, Nk, d, float(scale), _dt(q), _stream()), "mdx_attention")
+                            heads, Nq, Nk, d, float(scale), _dt(q), int(causal), _stream()), "mdx_attention")
     return out
 
 
