@@ -61,6 +61,16 @@ class Tensor(torch.Tensor):
             self.copy_(value)
         return self
 
+    def view(self, *shape):  # MindSpore's Tensor.view reshapes (copies when the layout requires it)
+        if len(shape) == 1 and isinstance(shape[0], torch.dtype):
+            return torch.Tensor.view(self, shape[0])
+        return self.reshape(*shape)
+
+    def transpose(self, *axes):  # MindSpore: a permutation (tuple or varargs), not torch's two-axis swap
+        if len(axes) == 1 and isinstance(axes[0], (tuple, list)):
+            axes = tuple(axes[0])
+        return self.permute(*axes)
+
 
 def tensor(data, dtype=None):
     return Tensor(data, dtype)
@@ -111,6 +121,11 @@ class Cell(torch.nn.Module):
 
     def to_float(self, dtype):
         return _set_to_float(self, dtype)
+
+    param_prefix = ""
+
+    def update_parameters_name(self, prefix="", recurse=True):  # torch names come from the attribute path already
+        return None
 
     def set_train(self, mode=True):
         return self.train(mode)
@@ -219,6 +234,9 @@ class SequentialCell(torch.nn.Sequential):
 
 
 class CellList(torch.nn.ModuleList):
+    def __init__(self, modules=None, auto_prefix=True):
+        super().__init__(modules)
+
     def to_float(self, dtype):
         return _set_to_float(self, dtype)
 
@@ -228,10 +246,24 @@ class MSELoss(Cell):
         super().__init__()
 
 
+class Sigmoid(Cell):
+    def construct(self, x):
+        return _wrap(torch.sigmoid(x))
+
+
+class Softmax(Cell):
+    def __init__(self, axis=-1):
+        super().__init__()
+        self.axis = axis
+
+    def construct(self, x):
+        return _wrap(torch.softmax(x, dim=self.axis))
+
+
 for _n, _c in dict(Cell=Cell, Dense=Dense, Conv2d=Conv2d, Conv1d=_Unused, Conv3d=_Unused, AvgPool1d=_Unused,
                    AvgPool2d=_Unused, Embedding=_Unused, GroupNorm=GroupNorm, LayerNorm=LayerNorm, SiLU=SiLU, GELU=GELU,
                    Dropout=Dropout, SequentialCell=SequentialCell, Sequential=SequentialCell, CellList=CellList,
-                   MSELoss=MSELoss).items():
+                   MSELoss=MSELoss, Softmax=Softmax, Sigmoid=Sigmoid, Pad=_Unused).items():
     setattr(nn, _n, _c)
 
 # ---------------------------------------------------------------------------------------------------------
@@ -274,6 +306,7 @@ def _broadcast_to(x, shape):
 
 
 _fns = dict(
+    bmm=torch.bmm, tanh=torch.tanh, transpose=lambda x, perm: x.permute(*perm),
     exp=torch.exp, expm1=torch.expm1, log=torch.log, sqrt=torch.sqrt, abs=torch.abs, sin=torch.sin, cos=torch.cos,
     pow=torch.pow, maximum=lambda a, b: torch.maximum(torch.as_tensor(a), torch.as_tensor(b)),
     minimum=lambda a, b: torch.minimum(torch.as_tensor(a), torch.as_tensor(b)),
@@ -309,6 +342,11 @@ _prims = dict(
     Sigmoid=lambda s, x: torch.sigmoid(x),
     GeLU=lambda s, x: F.gelu(x, approximate="tanh"),
     Identity=lambda s, x: x,
+    Exp=lambda s, x: torch.exp(x),
+    Squeeze=lambda s, x: x.squeeze(s.a[0] if s.a else s.k.get("axis", ())),
+    Gather=lambda s, params, idx, axis: torch.index_select(params, axis, idx.reshape(-1).long()).reshape(
+        tuple(params.shape[:axis]) + tuple(idx.shape) + tuple(params.shape[axis + 1:])),
+    AvgPool=lambda s, *a: (_ for _ in ()).throw(NotImplementedError("shim")),
     ExpandDims=lambda s, x, axis: x.unsqueeze(axis),
     Equal=lambda s, a, b: torch.eq(a, b),
     IsNan=lambda s, x: torch.isnan(x),
@@ -375,7 +413,17 @@ mnp.randn = lambda *shape: _wrap(torch.randn(*shape))
 initializer_mod = types.ModuleType("mindspore.common.initializer")
 
 
+class TruncatedNormal:
+    def __init__(self, sigma=0.01):
+        self.sigma = sigma
+
+
+initializer_mod.TruncatedNormal = TruncatedNormal
+
+
 def initializer(init, shape=None, dtype=float32):
+    if isinstance(init, TruncatedNormal):  # values are overwritten by the seeded weights anyway
+        return Tensor(torch.randn(_shape(shape)).clamp_(-2, 2) * init.sigma, dtype)
     if init == "zeros":
         return Tensor(torch.zeros(_shape(shape), dtype=dtype))
     if init == "ones":
@@ -403,6 +451,8 @@ def install():
     sys.modules["mindspore"] = ms
     sys.modules["mindspore.nn"] = nn
     sys.modules["mindspore.ops"] = ops
+    ops.operations = ops
+    sys.modules["mindspore.ops.operations"] = ops
     sys.modules["mindspore.numpy"] = mnp
     sys.modules["mindspore.common"] = common_mod
     sys.modules["mindspore.common.initializer"] = initializer_mod
