@@ -237,6 +237,58 @@ int mdx_sampler_dpmpp2m_step(const void* eps_model, int64_t ld_eps, int32_t mode
                              float* x_next, float* x0_cur, int32_t B, int32_t C, int32_t h, int32_t w,
                              void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Taichu-GLIDE family (vision/Taichu-GLIDE/model/glide_text2im): the operators its UNet / sampler need beyond
+ * the latent-diffusion set above.
+ *
+ * mdx_groupnorm_film — ResBlock with use_scale_shift_norm (model/unet.py:189-194):
+ *      out = GroupNorm(x) * (1 + scale) + shift, optional SiLU (out_layers_1).  scale_shift: fp32 rows
+ *      [n][scale(C) | shift(C)] with row stride ld_ss (the emb_layers output, split at unet.py:190).  Other
+ *      arguments as mdx_groupnorm (single source, no raw copy).
+ * mdx_avgpool2x2 — Downsample without conv, nn.AvgPool2d(2, 2) (unet.py:69-73; resblock_updown h_upd/x_upd) on NHWC.
+ * mdx_copy_rows — dst[b][r][:] = src[b][r][:] for b < n_batch, r < rows, width_bytes per row; all strides in
+ *      bytes, multiples of 16.  batch_stride_src_bytes = 0 broadcasts one block of rows.  Builds the
+ *      [encoder K/V | spatial K/V] sequences of QKVAttention (unet.py:262-266, ops.Concat(axis=-1)) and
+ *      CombinePrompt's broadcast of the per-step random prompt (guider.py:36-41).
+ * mdx_embedding_masked — Text2ImUNet.get_text_emb (text2im_model.py:79-84):
+ *      out[i] = mask[i] ? table[ids[i]] + pos[i % L] : pad[i % L]   (mask NULL => all ones)
+ * mdx_resize_bilinear — ops.ResizeBilinear(size, align_corners=False) (text2im_model.py:166,191) on fp32 NCHW;
+ *      quantize_u8 != 0 first applies PMeanVariance.superResPreprocess (gaussian_diffusion.py:224-230):
+ *      round((v + 1) * 127.5) / 127.5 - 1 to every source pixel.
+ * mdx_nchw2_to_nhwc_pad — mdx_nchw_to_nhwc_pad over ops.Concat(axis=1)((x1, x2)) (text2im_model.py:192).
+ * mdx_sampler_glide_step — Guider + PMeanVariance + PSample / DDimSample in one pass
+ *      (guider.py:60-70, gaussian_diffusion.py:158-181, :49-63, :82-103).
+ *      model_out: NHWC [cfg ? 2P : P, h, w, >= 2C]: channels [0,C) eps, [C,2C) variance fraction v; rows [0,P) are
+ *      the prompt half, [P,2P) the random-prompt half (guider.py:63: cond first — the opposite of plms.py).
+ *      eps   = cfg ? e_u + scale*(e_c - e_u) : e_c
+ *      x0    = clip(c[0]*x - c[1]*eps, -1, 1)                    (c[0] = sqrt(1/abar), c[1] = sqrt(1/abar - 1))
+ *      mode 0 (ancestral): logvar = f*c[5] + (1-f)*c[4], f = (v+1)/2 read from the prompt half;
+ *                          x_prev = c[2]*x0 + c[3]*x + c[9] * exp(0.5*logvar) * noise
+ *      mode 1 (DDIM):      e' = (c[0]*x - x0)/c[1]; sigma = c[8]*sqrt((1-c[7])/(1-c[6]))*sqrt((1-c[6])/c[7]);
+ *                          x_prev = sqrt(1-c[7]-sigma^2)*e' + sqrt(c[7])*x0 + c[9]*sigma*noise
+ *      coef_host[10] = {sqrt_recip_abar, sqrt_recipm1_abar, post_coef1, post_coef2, min_log, max_log, abar,
+ *                       abar_prev, eta, t != 0}.  x, noise, x_prev, pred_xstart: fp32 NCHW [P, C, h, w].
+ * --------------------------------------------------------------------------------------------------------- */
+int mdx_groupnorm_film(const void* x, int64_t ldx, int32_t C, int32_t n, int32_t HW, int32_t groups, float eps,
+                       const float* gamma, const float* beta, const float* scale_shift, int64_t ld_ss, int32_t silu,
+                       void* out, int64_t ldo, int32_t in_dtype, int32_t out_dtype, double* stats_scratch,
+                       void* stream);
+int mdx_avgpool2x2(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, void* out, int32_t in_dtype,
+                   int32_t out_dtype, void* stream);
+int mdx_copy_rows(const void* src, int64_t ld_src_bytes, int64_t batch_stride_src_bytes, void* dst,
+                  int64_t ld_dst_bytes, int64_t batch_stride_dst_bytes, int32_t n_batch, int32_t rows,
+                  int64_t width_bytes, void* stream);
+int mdx_embedding_masked(const float* table, int32_t vocab, int32_t width, const float* pos, const float* pad,
+                         int32_t L, const int32_t* ids, const int32_t* mask, int32_t n, void* out, int32_t dtype,
+                         void* stream);
+int mdx_resize_bilinear(const float* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t OH, int32_t OW,
+                        int32_t quantize_u8, float* out, void* stream);
+int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t C2, int32_t n, int32_t H, int32_t W,
+                          int32_t repeat, int32_t Cpad, void* out, int32_t dtype, void* stream);
+int mdx_sampler_glide_step(const void* model_out, int64_t ld_out, int32_t model_dtype, int32_t cfg, float scale,
+                           int32_t mode, const float* x, const float* coef_host, const float* noise, float* x_prev,
+                           float* pred_xstart, int32_t P, int32_t C, int32_t h, int32_t w, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmdx_b200.so")
-SOURCES = ["abi.cu", "gemm_tc.cu", "conv_direct.cu", "norm.cu", "attention.cu", "attention_tc.cu", "elementwise.cu", "rowops.cu", "sampler.cu"]
+SOURCES = ["abi.cu", "gemm_tc.cu", "conv_direct.cu", "norm.cu", "attention.cu", "attention_tc.cu", "elementwise.cu", "rowops.cu", "sampler.cu",
+           "glide_ops.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "--use_fast_math" if os.environ.get("MDX_FAST_MATH") else "-DMDX_PRECISE", "-I" + os.path.join(HERE, "..", "include")]

@@ -63,6 +63,7 @@ struct GnP {
   void* out; long long ldo;
   void* raw; long long ldraw;  // optional un-normalised copy of concat(x1, x2) in the out dtype
   double* stats;
+  const float* ss; long long ldss;  // optional FiLM rows [n][scale(C) | shift(C)]: y = gn(x) * (1 + scale) + shift
 };
 
 template <typename T>
@@ -178,6 +179,12 @@ __global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
     }
     a[i] = rstd_f * __ldg(p.gamma + c);
     b[i] = __ldg(p.beta + c) - mean_f * a[i];
+    if (p.ss) {
+      const float* row = p.ss + (long long)img * p.ldss;
+      const float sc = 1.f + __ldg(row + c);
+      a[i] *= sc;
+      b[i] = fmaf(b[i], sc, __ldg(row + p.C1 + p.C2 + c));
+    }
   }
   const int r0 = blockIdx.x * p.rows_per_block;
   const int r1 = min(p.HW, r0 + p.rows_per_block);
@@ -343,10 +350,10 @@ int launch_ln(const void* x, long long ldx, int rows, int C, float eps, const fl
 }  // namespace
 
 
-extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
-                             int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma,
-                             const float* beta, int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw,
-                             int32_t in_dtype, int32_t out_dtype, double* stats_scratch, void* stream) {
+static int gn_run(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2, int32_t n,
+                  int32_t HW, int32_t groups, float eps, const float* gamma, const float* beta, int32_t silu,
+                  void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
+                  const float* scale_shift, int64_t ld_ss, double* stats_scratch, void* stream) {
   MDX_CHECK_ARG(x1 && out && gamma && beta && stats_scratch, "mdx_groupnorm: NULL operand");
   MDX_CHECK_ARG(n > 0 && HW > 0 && C1 > 0 && C2 >= 0, "mdx_groupnorm: empty problem");
   MDX_CHECK_ARG(C2 == 0 || x2 != nullptr, "mdx_groupnorm: x2 is NULL but C2 > 0");
@@ -366,10 +373,28 @@ extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void
   p.n = n; p.HW = HW; p.groups = groups; p.cpg = C / groups; p.rows_per_block = 0;
   p.eps = eps; p.gamma = gamma; p.beta = beta; p.silu = silu; p.out = out; p.ldo = ldo;
   p.raw = raw_copy; p.ldraw = ldraw; p.stats = stats_scratch;
+  p.ss = scale_shift; p.ldss = ld_ss;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (in_dtype == MDX_BF16) return launch_gn<bf16, bf16>(p, st);
   if (out_dtype == MDX_BF16) return launch_gn<float, bf16>(p, st);
   return launch_gn<float, float>(p, st);
+}
+
+extern "C" int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2,
+                             int32_t n, int32_t HW, int32_t groups, float eps, const float* gamma,
+                             const float* beta, int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw,
+                             int32_t in_dtype, int32_t out_dtype, double* stats_scratch, void* stream) {
+  return gn_run(x1, ld1, C1, x2, ld2, C2, n, HW, groups, eps, gamma, beta, silu, out, ldo, raw_copy, ldraw, in_dtype,
+                out_dtype, nullptr, 0, stats_scratch, stream);
+}
+
+extern "C" int mdx_groupnorm_film(const void* x, int64_t ldx, int32_t C, int32_t n, int32_t HW, int32_t groups,
+                                  float eps, const float* gamma, const float* beta, const float* scale_shift,
+                                  int64_t ld_ss, int32_t silu, void* out, int64_t ldo, int32_t in_dtype,
+                                  int32_t out_dtype, double* stats_scratch, void* stream) {
+  MDX_CHECK_ARG(scale_shift && ld_ss >= 2 * (int64_t)C, "mdx_groupnorm_film: scale_shift rows must hold 2*C floats");
+  return gn_run(x, ldx, C, nullptr, 0, 0, n, HW, groups, eps, gamma, beta, silu, out, ldo, nullptr, 0, in_dtype,
+                out_dtype, scale_shift, ld_ss, stats_scratch, stream);
 }
 
 extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,

@@ -387,3 +387,106 @@ def sampler_dpmpp2m_step(eps_model, x, coef, cfg, scale, C, model_type=0, x0_pre
                                        ctypes.cast(_host_floats(coef), ctypes.c_void_p), _p(x_next), _p(x0_cur), B, C,
                                        h, wd, _stream()), "mdx_sampler_dpmpp2m_step")
     return x_next, x0_cur
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Taichu-GLIDE operators (include/mdx.h, "Taichu-GLIDE family")
+# ---------------------------------------------------------------------------------------------------------
+def groupnorm_film(x, gamma, beta, scale_shift, groups=32, eps=1e-5, silu=False, scratch=None, out_dtype=None):
+    """GroupNorm(x) * (1 + scale) + shift (+SiLU); scale_shift: fp32 [n, 2C] view (row stride may exceed 2C)."""
+    lib = _lib.load()
+    n = x.shape[0]
+    rows, C, ldx = _rows_ld(x)
+    if scale_shift.dtype != torch.float32 or scale_shift.stride(-1) != 1 or scale_shift.shape != (n, 2 * C):
+        raise ValueError("scale_shift must be float32 [n, 2C] with contiguous last dim")
+    out = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
+    if scratch is None:
+        scratch = torch.empty(n * groups * 2, dtype=torch.float64, device=x.device)
+    check(lib.mdx_groupnorm_film(_p(x), ldx, C, n, rows // n, groups, float(eps), _p(_f32(gamma, "gamma")),
+                                 _p(_f32(beta, "beta")), _p(scale_shift), scale_shift.stride(0), int(silu), _p(out),
+                                 C, _dt(x), _dt(out), _p(scratch), _stream()), "mdx_groupnorm_film")
+    return out
+
+
+def avgpool2x2(x, out_dtype=None):
+    lib = _lib.load()
+    n, H, W, C = x.shape
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    out = torch.empty((n, H // 2, W // 2, C), dtype=out_dtype or x.dtype, device=x.device)
+    check(lib.mdx_avgpool2x2(_p(x), n, H, W, C, _p(out), _dt(x), _dt(out), _stream()), "mdx_avgpool2x2")
+    return out
+
+
+def copy_rows(src, dst):
+    """dst[b, r, :] = src[b, r, :] for 3-D views [nb, rows, width] with contiguous last dim; src.shape[0] == 1
+    broadcasts."""
+    lib = _lib.load()
+    if src.dim() != 3 or dst.dim() != 3 or src.dtype != dst.dtype or src.stride(-1) != 1 or dst.stride(-1) != 1:
+        raise ValueError("copy_rows takes 3-D views of one dtype with contiguous last dim")
+    nb, rows, width = dst.shape
+    if src.shape[1:] != dst.shape[1:] or src.shape[0] not in (1, nb):
+        raise ValueError("copy_rows shape mismatch: %s -> %s" % (tuple(src.shape), tuple(dst.shape)))
+    es = src.element_size()
+    bs_src = 0 if (src.shape[0] == 1 and nb > 1) else src.stride(0) * es
+    check(lib.mdx_copy_rows(_p(src), src.stride(1) * es, bs_src, _p(dst), dst.stride(1) * es, dst.stride(0) * es, nb,
+                            rows, width * es, _stream()), "mdx_copy_rows")
+    return dst
+
+
+def embedding_masked(table, pos, pad, ids, mask=None, dtype=torch.float32):
+    """out[i] = mask[i] ? table[ids[i]] + pos[i % L] : pad[i % L]; ids/mask int32 [batch, L]."""
+    lib = _lib.load()
+    table, pos = _f32(table, "table"), _f32(pos, "pos")
+    for t, nm in ((ids, "ids"), (mask, "mask")):
+        if t is not None and (t.dtype != torch.int32 or not t.is_contiguous() or not t.is_cuda):
+            raise TypeError("%s must be a contiguous int32 CUDA tensor" % nm)
+    n, L, width = ids.numel(), pos.shape[0], table.shape[1]
+    out = torch.empty((n, width), dtype=dtype, device=table.device)
+    check(lib.mdx_embedding_masked(_p(table), table.shape[0], width, _p(pos), _p(_f32(pad, "pad")), L, _p(ids),
+                                   _p(mask), n, _p(out), _DT[dtype], _stream()), "mdx_embedding_masked")
+    return out
+
+
+def resize_bilinear(x, OH, OW, quantize_u8=False):
+    lib = _lib.load()
+    x = _f32(x, "x")
+    n, C, H, W = x.shape
+    out = torch.empty((n, C, OH, OW), dtype=torch.float32, device=x.device)
+    check(lib.mdx_resize_bilinear(_p(x), n, C, H, W, OH, OW, int(quantize_u8), _p(out), _stream()),
+          "mdx_resize_bilinear")
+    return out
+
+
+def nchw2_to_nhwc(x1, x2, dtype, repeat=1, cpad=None):
+    """NHWC (channel-padded) image of concat(x1, x2) along channels; x2 may be None."""
+    lib = _lib.load()
+    x1 = _f32(x1, "x1")
+    n, C1, H, W = x1.shape
+    C2 = 0
+    if x2 is not None:
+        x2 = _f32(x2, "x2")
+        if x2.shape[0] != n or x2.shape[2:] != x1.shape[2:]:
+            raise ValueError("x2 must match x1 in batch and size")
+        C2 = x2.shape[1]
+    cp = cpad or (C1 + C2)
+    out = torch.empty((n * repeat, H, W, cp), dtype=dtype, device=x1.device)
+    check(lib.mdx_nchw2_to_nhwc_pad(_p(x1), C1, _p(x2), C2, n, H, W, repeat, cp, _p(out), _DT[dtype], _stream()),
+          "mdx_nchw2_to_nhwc_pad")
+    return out
+
+
+def sampler_glide_step(model_out, x, coef, cfg, scale, mode, noise=None, x_prev=None, pred_xstart=None):
+    """model_out: NHWC [cfg?2P:P, h, w, ld>=2C]; x: fp32 NCHW [P, C, h, w]; coef: 10 floats (mdx.h)."""
+    lib = _lib.load()
+    P, C, h, wd = x.shape
+    x = _f32(x, "x")
+    if x_prev is None:
+        x_prev = torch.empty_like(x)
+    if not model_out.is_contiguous() or model_out.shape[0] != (2 * P if cfg else P):
+        raise ValueError("model_out must be contiguous NHWC with %d images" % (2 * P if cfg else P))
+    check(lib.mdx_sampler_glide_step(_p(model_out), model_out.shape[-1], _dt(model_out), int(cfg), float(scale),
+                                     int(mode), _p(x), ctypes.cast(_host_floats(coef), ctypes.c_void_p),
+                                     _p(_f32(noise, "noise")), _p(x_prev), _p(pred_xstart), P, C, h, wd, _stream()),
+          "mdx_sampler_glide_step")
+    return x_prev

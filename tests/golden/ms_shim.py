@@ -28,6 +28,8 @@ class Tensor(torch.Tensor):
 
     @staticmethod
     def __new__(cls, data=None, dtype=None, *args, **kwargs):
+        if data is None and "input_data" in kwargs:
+            data = kwargs.pop("input_data")
         if isinstance(data, torch.Tensor):
             t = data.detach().clone()
         elif isinstance(data, np.ndarray):
@@ -169,6 +171,58 @@ class Conv2d(Cell):
                               dilation=self.dilation, groups=self.group))
 
 
+class Conv1d(Cell):
+    """nn.Conv1d keeps a 4-D weight [out, in, 1, k] (it runs on Conv2D internally)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, pad_mode="same", padding=0, dilation=1,
+                 group=1, has_bias=False, weight_init="normal", bias_init="zeros"):
+        super().__init__()
+        if pad_mode not in ("pad", "valid") and kernel_size != 1:
+            raise NotImplementedError("shim: Conv1d pad_mode=%r" % pad_mode)
+        self.stride, self.padding = stride, (padding if pad_mode == "pad" else 0)
+        self.weight = Parameter(torch.randn(out_channels, in_channels // group, 1, kernel_size) * 0.01)
+        self.bias = Parameter(torch.zeros(out_channels)) if has_bias else None
+
+    def construct(self, x):
+        w = self.weight.reshape(self.weight.shape[0], self.weight.shape[1], -1)
+        return _wrap(F.conv1d(x, w, self.bias, stride=self.stride, padding=self.padding))
+
+
+class AvgPool2d(Cell):
+    def __init__(self, kernel_size=1, stride=1, pad_mode="valid"):
+        super().__init__()
+        self.k, self.s = kernel_size, stride
+
+    def construct(self, x):
+        return _wrap(F.avg_pool2d(x, self.k, self.s))
+
+
+class Embedding(Cell):
+    def __init__(self, vocab_size, embedding_size, use_one_hot=False, embedding_table="normal", dtype=None,
+                 padding_idx=None):
+        super().__init__()
+        self.embedding_table = Parameter(torch.randn(vocab_size, embedding_size) * 0.01)
+
+    def construct(self, ids):
+        return _wrap(self.embedding_table[ids.long()])
+
+
+class _Linear(Cell):
+    """mindspore.nn.transformer.layers._Linear: weight [out, in] (transpose_b=True), y = x W^T + b on the last axis."""
+
+    def __init__(self, in_channels, out_channels, weight_init="normal", bias_init="zeros", has_bias=True,
+                 activation=None, transpose_b=True, expert_num=1, outer_batch=1, expert_group_size=None,
+                 param_init_type=None, compute_dtype=None):
+        super().__init__()
+        self.weight = Parameter(torch.randn(out_channels, in_channels) * 0.01)
+        self.bias = Parameter(torch.zeros(out_channels))
+        self.compute_dtype = compute_dtype
+
+    def construct(self, x):
+        dt = self.compute_dtype or x.dtype
+        return _wrap(F.linear(x.to(dt), self.weight.to(dt), self.bias.to(dt)))
+
+
 class _Unused(Cell):
     def __init__(self, *a, **k):
         super().__init__()
@@ -260,8 +314,8 @@ class Softmax(Cell):
         return _wrap(torch.softmax(x, dim=self.axis))
 
 
-for _n, _c in dict(Cell=Cell, Dense=Dense, Conv2d=Conv2d, Conv1d=_Unused, Conv3d=_Unused, AvgPool1d=_Unused,
-                   AvgPool2d=_Unused, Embedding=_Unused, GroupNorm=GroupNorm, LayerNorm=LayerNorm, SiLU=SiLU, GELU=GELU,
+for _n, _c in dict(Cell=Cell, Dense=Dense, Conv2d=Conv2d, Conv1d=Conv1d, Conv3d=_Unused, AvgPool1d=_Unused,
+                   AvgPool2d=AvgPool2d, Embedding=Embedding, GroupNorm=GroupNorm, LayerNorm=LayerNorm, SiLU=SiLU, GELU=GELU,
                    Dropout=Dropout, SequentialCell=SequentialCell, Sequential=SequentialCell, CellList=CellList,
                    MSELoss=MSELoss, Softmax=Softmax, Sigmoid=Sigmoid, Pad=_Unused).items():
     setattr(nn, _n, _c)
@@ -305,6 +359,20 @@ def _broadcast_to(x, shape):
     return torch.as_tensor(x).expand(*_shape(shape)) if -1 not in shape else x.expand(*shape)
 
 
+def _resize_bilinear_legacy(x, size):
+    """ops.ResizeBilinear(size, align_corners=False) with its default half_pixel_centers=False: src = dst * in/out."""
+    OH, OW = int(size[0]), int(size[1])
+    H, W = x.shape[-2], x.shape[-1]
+    fy = torch.arange(OH, dtype=torch.float32) * (np.float32(H) / np.float32(OH))
+    fx = torch.arange(OW, dtype=torch.float32) * (np.float32(W) / np.float32(OW))
+    y0, x0 = fy.floor().long(), fx.floor().long()
+    y1, x1 = (y0 + 1).clamp(max=H - 1), (x0 + 1).clamp(max=W - 1)
+    wy, wx = (fy - y0)[:, None], (fx - x0)[None, :]
+    top = x[..., y0, :][..., x0] * (1 - wx) + x[..., y0, :][..., x1] * wx
+    bot = x[..., y1, :][..., x0] * (1 - wx) + x[..., y1, :][..., x1] * wx
+    return top * (1 - wy) + bot * wy
+
+
 _fns = dict(
     bmm=torch.bmm, tanh=torch.tanh, transpose=lambda x, perm: x.permute(*perm),
     exp=torch.exp, expm1=torch.expm1, log=torch.log, sqrt=torch.sqrt, abs=torch.abs, sin=torch.sin, cos=torch.cos,
@@ -330,7 +398,14 @@ ops.dropout = _not_on_path
 ops.value_and_grad = _not_on_path
 
 _prims = dict(
-    Cast=lambda s, x, dt: x.to(dt),
+    Cast=lambda s, x, dt: torch.as_tensor(x).to(dt),
+    Slice=lambda s, x, begin, size: x[tuple(slice(int(b), int(b) + int(n)) for b, n in zip(begin, size))],
+    BroadcastTo=lambda s, x: torch.as_tensor(x).expand(*_shape(s.a[0])),
+    Ones=lambda s, shape, dtype=float32: torch.ones(_shape(shape), dtype=dtype),
+    Mul=lambda s, a, b: a * b, Add=lambda s, a, b: a + b, Div=lambda s, a, b: a / b, Neg=lambda s, x: -x,
+    Round=lambda s, x: torch.round(x), Sin=lambda s, x: torch.sin(x), Print=lambda s, *a: None,
+    UniformReal=lambda s, shape: torch.rand(_shape(shape)),
+    ResizeBilinear=lambda s, x: _resize_bilinear_legacy(x, s.a[0]),
     Zeros=lambda s, shape, dtype=float32: torch.zeros(_shape(shape), dtype=dtype),
     ZerosLike=lambda s, x: torch.zeros_like(x),
     Transpose=lambda s, x, perm: x.permute(*perm),
@@ -401,7 +476,12 @@ def _full(shape, fill_value, dtype=None):
 
 
 mnp.full = _full
-mnp.where = lambda c, a, b: _wrap(torch.where(c, torch.as_tensor(a), torch.as_tensor(b)))
+mnp.where = lambda c, a, b: _wrap(torch.where(c.bool(), torch.as_tensor(a), torch.as_tensor(b)))
+mnp.empty = lambda shape, dtype=float32: _wrap(torch.zeros(_shape(shape), dtype=dtype))
+mnp.zeros = lambda shape, dtype=float32: _wrap(torch.zeros(_shape(shape), dtype=dtype))
+mnp.ones = lambda shape, dtype=float32: _wrap(torch.ones(_shape(shape), dtype=dtype))
+mnp.randint = lambda lo, hi=None, shape=(), dtype=int32: _wrap(torch.randint(lo, hi, _shape(shape)).to(dtype))
+mnp.choose = lambda a, choices: _wrap(torch.as_tensor(choices)[a.long()])
 mnp.tile = lambda x, reps: _wrap(torch.tile(x, tuple(reps) if isinstance(reps, (tuple, list)) else (reps,)))
 mnp.flip = lambda x, axis=None: _wrap(torch.flip(x, dims=list(range(x.dim())) if axis is None else [axis]))
 mnp.array = lambda data, dtype=None: Tensor(data, dtype)
@@ -451,6 +531,13 @@ def install():
     sys.modules["mindspore"] = ms
     sys.modules["mindspore.nn"] = nn
     sys.modules["mindspore.ops"] = ops
+    tr = types.ModuleType("mindspore.nn.transformer")
+    trl = types.ModuleType("mindspore.nn.transformer.layers")
+    trl._Linear = _Linear
+    tr.layers = trl
+    nn.transformer = tr
+    sys.modules["mindspore.nn.transformer"] = tr
+    sys.modules["mindspore.nn.transformer.layers"] = trl
     ops.operations = ops
     sys.modules["mindspore.ops.operations"] = ops
     sys.modules["mindspore.numpy"] = mnp

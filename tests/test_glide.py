@@ -1,0 +1,281 @@
+"""Taichu-GLIDE: text-conditioned pixel-space UNet with its per-step text transformer,
+guided ancestral sampling with learned sigma, and the DDIM upsampler.
+
+CPU tier: the oracle (oracle/glide.py) and the host-side schedule code against golden vectors from the executed
+reference (tests/golden/make_golden_glide.py).  GPU tier: the CUDA path against the same goldens.
+Tolerances: fp32 check mode 1e-4 of the output range per network evaluation (north star), 5e-4 after the chained
+loops; bf16 2e-2 of the range per evaluation and cosine >= 0.999 on the loop results (north star: final latents)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+
+BASE = dict(image_size=16, num_channels=64, num_res_blocks=1, channel_mult=(1, 2), attention_resolutions=(1, 2),
+            xf_width=128, xf_layers=2, xf_heads=2, n_vocab=1000, timestep_respacing="1,1,1,1,1,2")
+UP = dict(image_size=32, num_channels=64, num_res_blocks=1, channel_mult=(1, 2), attention_resolutions=(2,),
+          xf_width=128, xf_layers=2, xf_heads=2, n_vocab=1000)
+PICS, SCALE = 2, 3.0
+
+
+def golden():
+    return dict(np.load(os.path.join(ROOT, "tests", "golden", "glide_golden.npz")))
+
+
+def options(dtype=torch.bfloat16):
+    from minddiffusion_b200 import glide
+    return glide.model_and_diffusion_defaults(dtype=dtype, **BASE), glide.model_and_diffusion_upsample(dtype=dtype, **UP)
+
+
+def rel(a, b):
+    a = a.detach().float().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+    b = b.detach().float().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
+    return float(np.abs(a.astype(np.float64) - b).max() / (np.abs(b).max() + 1e-30))
+
+
+def cosine(a, b):
+    a = a.detach().float().cpu().numpy().ravel().astype(np.float64)
+    b = np.asarray(b).ravel().astype(np.float64)
+    return float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b)))
+
+
+def T_(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU tier
+# ------------------------------------------------------------------------------------------------------------
+def test_schedules_match_executed_reference():
+    from minddiffusion_b200 import glide
+    from oracle import glide as og
+    G = golden()
+    for tag, name, resp in (("base", "squaredcos_cap_v2", "60"), ("up", "linear", "fast27")):
+        use = glide.space_timesteps(1000, resp)
+        tmap, nb = glide.space_diffusion_from_base(use, glide.alpha_calculator(glide.get_named_beta_schedule(name, 1000)))
+        assert np.array_equal(np.array(tmap), G["sched_%s_map" % tag])            # integer work: exact
+        np.testing.assert_allclose(nb, G["sched_%s_betas" % tag], rtol=1e-12, atol=0)
+        assert og.spaced_steps(1000, resp) == use
+        tb = og.Tables(name, 1000, resp)
+        assert tb.timestep_map == tmap
+        np.testing.assert_allclose(tb.betas, np.array(nb, dtype=np.float32), rtol=0, atol=0)
+    assert len(glide.space_timesteps(1000, "ddim50")) == 50
+    assert sorted(glide.space_timesteps(1000, "fast27"))[-3:] == [799, 800, 997]
+    with pytest.raises(ValueError):
+        glide.space_timesteps(10, "6,6")
+
+
+def test_parameter_inventory():
+    from minddiffusion_b200 import glide
+    count = lambda S: sum(int(np.prod(s)) for s in S.values())
+    nb = count(glide.glide_param_shapes(glide.model_and_diffusion_defaults(), 3))
+    nu = count(glide.glide_param_shapes(glide.model_and_diffusion_upsample(), 6))
+    assert 384e6 < nb < 386e6 and 397e6 < nu < 400e6       # GLIDE text2im 64x64: 385 M; upsampler: 398 M
+    inp, mid, out = glide.glide_structure(glide.model_and_diffusion_defaults(), 3)
+    assert len(inp) == 1 + 4 * 3 + 3 and len(out) == 16 and sum(l[0] == "attn" for b in inp for l in b) == 9
+
+
+def test_oracle_unet_matches_executed_reference():
+    from minddiffusion_b200 import glide
+    from oracle import glide as og
+    G = golden()
+    ob, ou = options()
+    out = og.unet_forward(glide.random_glide_params(ob, 3, seed=0), ob, T_(G["base_x"]), T_(G["base_t"]),
+                          T_(G["base_tok"]), T_(G["base_mask"]))
+    assert rel(out, G["base_out"]) < 1e-5
+    out = og.unet_forward(glide.random_glide_params(ou, 6, seed=1), ou, T_(G["up_x"]), T_(G["up_t"]), T_(G["up_tok"]),
+                          T_(G["up_mask"]), low_res=T_(G["up_low"]))
+    assert rel(out, G["up_out"]) < 1e-5
+
+
+def test_oracle_sampling_loops_match_executed_reference():
+    from minddiffusion_b200 import glide
+    from oracle import glide as og
+    G = golden()
+    ob, ou = options()
+    out = og.p_sample_loop(glide.random_glide_params(ob, 3, seed=0), ob, T_(G["base_tok"]), T_(G["base_mask"]),
+                           T_(G["loop_xT"]), SCALE, T_(G["loop_tokens"]), T_(G["loop_noise"]))
+    assert rel(out, G["loop_out"]) < 1e-4
+    out = og.ddim_loop(glide.random_glide_params(ou, 6, seed=1), ou, T_(G["up_low"]), T_(G["up_tok"]),
+                       T_(G["up_mask"]), T_(G["ddim_xT"]))
+    assert rel(out, G["ddim_out"]) < 1e-4
+
+
+def test_head_permutation_is_the_reference_split():
+    """QKVAttention reshapes [N, H*3*C, T] to [N*H, 3*C, T] and splits; the fused layout is [part][head][i]."""
+    from minddiffusion_b200.glide import _head_perm
+    heads, ch = 3, 4
+    w = torch.arange(heads * 3 * ch)
+    q, k, v = torch.chunk(w.reshape(heads, 3 * ch), 3, dim=1)
+    assert torch.equal(w[_head_perm(heads, ch, 3)], torch.cat((q.reshape(-1), k.reshape(-1), v.reshape(-1))))
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GPU tier
+# ------------------------------------------------------------------------------------------------------------
+MODES = [(torch.float32, 1e-4, 5e-4), (torch.bfloat16, 2e-2, None)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol,tol_loop", MODES, ids=["fp32", "bf16"])
+def test_cuda_unets_against_goldens(dtype, tol, tol_loop):
+    from minddiffusion_b200 import glide
+    G = golden()
+    ob, ou = options(dtype)
+    base = glide.create_model(glide.random_glide_params(ob, 3, seed=0), **ob)
+    out = base(T_(G["base_x"]).cuda(), T_(G["base_t"]).cuda(), T_(G["base_tok"]).cuda(), T_(G["base_mask"]).cuda())
+    assert tuple(out.shape) == (4, 6, 16, 16) and out.dtype == torch.float32
+    assert rel(out, G["base_out"]) < tol
+    up = glide.create_upsample_model(glide.random_glide_params(ou, 6, seed=1), **ou)
+    out = up(T_(G["up_x"]).cuda(), T_(G["up_t"]).cuda(), T_(G["up_low"]).cuda(), T_(G["up_tok"]).cuda(),
+             T_(G["up_mask"]).cuda())
+    assert tuple(out.shape) == (2, 6, 32, 32)
+    assert rel(out, G["up_out"]) < tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol,tol_loop", MODES, ids=["fp32", "bf16"])
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "graph"])
+def test_cuda_sampling_loops_against_goldens(dtype, tol, tol_loop, graph):
+    from minddiffusion_b200 import glide
+    G = golden()
+    ob, ou = options(dtype)
+    dm = glide.init_diffusion_model(ob, SCALE, (2 * PICS, 3, 16, 16), params=glide.random_glide_params(ob, 3, seed=0))
+    assert dm.model.dtype == dtype
+    dm.model.use_cuda_graph = graph
+    out = glide.gaussian_p_sample_loop(dm, T_(G["base_tok"]).cuda(), T_(G["base_mask"]).cuda(), (2 * PICS, 3, 16, 16),
+                                       dm.num_timesteps, text_ctx=128, noise=T_(G["loop_xT"]).cuda(),
+                                       vocab_len=ob["n_vocab"], random_tokens=T_(G["loop_tokens"]),
+                                       step_noise=T_(G["loop_noise"][:, :PICS]))
+    assert tuple(out.shape) == (2 * PICS, 3, 16, 16)
+    want = G["loop_out"][:PICS]
+    if tol_loop is not None:
+        assert rel(out[:PICS], want) < tol_loop
+    assert cosine(out[:PICS], want) >= 0.999
+    sm = glide.init_super_res_model(ou, (PICS, 3, 32, 32), params=glide.random_glide_params(ou, 6, seed=1))
+    sm.model.use_cuda_graph = graph
+    out = glide.ddim_sample_loop(sm, (PICS, 3, 32, 32), T_(G["up_low"]).cuda(), T_(G["up_tok"]).cuda(),
+                                 T_(G["up_mask"]).cuda(), sm.num_timesteps, noise=T_(G["ddim_xT"]).cuda())
+    assert sm.num_timesteps == int(G["ddim_steps"]) == 27
+    if tol_loop is not None:
+        assert rel(out, G["ddim_out"]) < tol_loop
+    assert cosine(out, G["ddim_out"]) >= 0.999
+
+
+@pytest.mark.gpu
+def test_reference_call_signature_of_the_diffusion_models():
+    """diffusion_model(x, timesteps, token, mask, random_token, random_mask) -> (sample, pred_xstart), x of shape
+    [2 * pics, ...] as in main_funcs.py:36-38; one step must equal the first step of the loop."""
+    from minddiffusion_b200 import glide
+    G = golden()
+    ob, _ = options()
+    dm = glide.init_diffusion_model(ob, SCALE, (2 * PICS, 3, 16, 16), params=glide.random_glide_params(ob, 3, seed=0))
+    tok, mask = T_(G["base_tok"]).cuda(), T_(G["base_mask"]).cuda()
+    i = dm.num_timesteps - 1
+    x = T_(G["loop_xT"]).cuda()
+    sample, x0 = dm(x, torch.tensor([i], dtype=torch.int32), tok, mask, T_(G["loop_tokens"][i]).cuda(),
+                    torch.ones(128, dtype=torch.int32).cuda(), noise=T_(G["loop_noise"][i]).cuda())
+    assert tuple(sample.shape) == (2 * PICS, 3, 16, 16) and torch.equal(sample[:PICS], sample[PICS:])
+    assert float(x0.abs().max()) <= 1.0
+    with pytest.raises(IndexError):
+        dm(x, torch.tensor([dm.num_timesteps]), tok, mask, T_(G["loop_tokens"][0]).cuda())
+
+
+@pytest.mark.gpu
+def test_glide_kernels_against_torch():
+    """The GLIDE-only operators against plain torch fp32 (bit-exact where the arithmetic allows)."""
+    import torch.nn.functional as F
+    from minddiffusion_b200 import ops
+    from oracle import glide as og
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, 6, 8, 64, generator=g).cuda()
+    ref = F.avg_pool2d(x.permute(0, 3, 1, 2), 2, 2).permute(0, 2, 3, 1)
+    assert torch.allclose(ops.avgpool2x2(x), ref, atol=1e-6)
+    assert rel(ops.avgpool2x2(x, out_dtype=torch.bfloat16), ref) < 1e-2
+    # FiLM group norm
+    gamma, beta = torch.randn(64, generator=g).cuda(), torch.randn(64, generator=g).cuda()
+    ss = torch.randn(2, 128, generator=g).cuda()
+    y = F.group_norm(x.permute(0, 3, 1, 2), 32, gamma, beta, 1e-5)
+    y = F.silu(y * (1 + ss[:, :64, None, None]) + ss[:, 64:, None, None]).permute(0, 2, 3, 1)
+    assert rel(ops.groupnorm_film(x, gamma, beta, ss, silu=True), y) < 1e-5
+    # strided / broadcast row copies are exact
+    src = torch.randn(3, 5, 24, generator=g).cuda()
+    dst = torch.zeros(3, 9, 16).cuda()
+    ops.copy_rows(src[:, :, 8:], dst[:, 4:, :])
+    assert torch.equal(dst[:, 4:], src[:, :, 8:]) and float(dst[:, :4].abs().max()) == 0.0
+    ops.copy_rows(src[:1, :, 8:], dst[:, :5, :])
+    assert torch.equal(dst[2, :5], src[0, :, 8:])
+    # masked embedding
+    table, pos, pad = torch.randn(50, 16, generator=g).cuda(), torch.randn(8, 16, generator=g).cuda(), torch.randn(8, 16, generator=g).cuda()
+    ids = torch.randint(0, 50, (3, 8), generator=g).int().cuda()
+    mask = (torch.rand(3, 8, generator=g) > 0.4).int().cuda()
+    ref = torch.where(mask.bool()[..., None], table[ids.long()] + pos[None], pad[None]).reshape(24, 16)
+    assert torch.equal(ops.embedding_masked(table, pos, pad, ids, mask), ref)
+    # bilinear resize (legacy coordinates) and the uint8 quantisation of the sampler
+    low = (torch.rand(2, 3, 16, 16, generator=g) * 2 - 1)
+    assert rel(ops.resize_bilinear(low.cuda(), 64, 64), og.resize_bilinear_legacy(low, (64, 64))) < 1e-6
+    q = torch.round((low + 1) * 127.5) / 127.5 - 1
+    assert rel(ops.resize_bilinear(low.cuda(), 40, 40, True), og.resize_bilinear_legacy(q, (40, 40))) < 1e-6
+    # concat + NHWC + pad
+    a, b = torch.randn(2, 3, 4, 4, generator=g), torch.randn(2, 3, 4, 4, generator=g)
+    o = ops.nchw2_to_nhwc(a.cuda(), b.cuda(), torch.float32, repeat=2, cpad=8)
+    want = torch.cat((a, b, torch.zeros(2, 2, 4, 4)), 1).permute(0, 2, 3, 1).repeat(2, 1, 1, 1)
+    assert torch.equal(o.cpu(), want)
+
+
+@pytest.mark.gpu
+def test_glide_step_kernel_matches_oracle_arithmetic():
+    from minddiffusion_b200 import glide, ops
+    from oracle import glide as og
+    ob, _ = options()
+    tb, T = glide.DiffusionTables(ob), og.Tables(ob["noise_schedule"], 1000, ob["timestep_respacing"])
+    g = torch.Generator().manual_seed(3)
+    P = 2
+    out = torch.randn(2 * P, 6, 8, 8, generator=g)
+    x, nz = torch.randn(P, 3, 8, 8, generator=g), torch.randn(P, 3, 8, 8, generator=g)
+    nhwc = out.permute(0, 2, 3, 1).contiguous().cuda()
+    for i in (3, 1, 0):
+        eps, rest = out[:, :3], out[:, 3:]
+        he = eps[P:] + SCALE * (eps[:P] - eps[P:])
+        mean, logvar, x0, eps2 = og.p_mean_variance(T, torch.cat((he, rest[:P]), 1), x, i)
+        want = mean + (0.0 if i == 0 else 1.0) * torch.exp(0.5 * logvar) * nz
+        x0_k = torch.empty(P, 3, 8, 8).cuda()
+        got = ops.sampler_glide_step(nhwc, x.cuda(), tb.step_coef(i), True, SCALE, 0, noise=nz.cuda(), pred_xstart=x0_k)
+        assert rel(got, want) < 1e-5 and rel(x0_k, x0) < 1e-5
+        # DDIM (no guidance): rows [0, P)
+        m2 = out[:P]
+        _, _, x0d, e2 = og.p_mean_variance(T, m2, x, i)
+        wantd = torch.sqrt(1 - T.ac_prev_t[i]) * e2 + x0d * torch.sqrt(T.ac_prev_t[i])
+        gotd = ops.sampler_glide_step(m2.permute(0, 2, 3, 1).contiguous().cuda(), x.cuda(), tb.step_coef(i, 0.0), False,
+                                      1.0, 1)
+        assert rel(gotd, wantd) < 1e-5
+
+
+@pytest.mark.gpu
+def test_cuda_glide_shipped_architectures_bf16():
+    """The shipped option sets (192 channels: 6-channel GroupNorm groups, 576/768-wide levels, 16-layer text
+    transformer, 9+ attention blocks with 64-wide heads) for one evaluation against the oracle.  The upsampler runs
+    at 128x128 instead of 256x256 to keep the CPU oracle within seconds; its layer stack is unchanged."""
+    from minddiffusion_b200 import glide
+    from oracle import glide as og
+    rs = np.random.RandomState(5)
+    for opts, cin, size, low in ((glide.model_and_diffusion_defaults(), 3, 64, None),
+                                 (glide.model_and_diffusion_upsample(image_size=128), 6, 128, 32)):
+        P = glide.random_glide_params(opts, cin, seed=2)
+        n = 2 if low is None else 1
+        x = torch.from_numpy(rs.randn(n, 3, size, size).astype(np.float32))
+        t = torch.tensor([801.0, 33.0][:n])
+        tok = torch.from_numpy(rs.randint(1, opts["n_vocab"] - 1, size=(n, 128)).astype(np.int32))
+        mask = torch.zeros(n, 128, dtype=torch.int32)
+        mask[:, :21] = 1
+        if low is None:
+            ref = og.unet_forward(P, opts, x, t, tok, mask)
+            out = glide.create_model(P, **opts)(x.cuda(), t.cuda(), tok.cuda(), mask.cuda())
+        else:
+            lr = torch.from_numpy(np.clip(rs.randn(n, 3, low, low) * 0.5, -1, 1).astype(np.float32))
+            ref = og.unet_forward(P, opts, x, t, tok, mask, low_res=lr)
+            out = glide.create_upsample_model(P, **opts)(x.cuda(), t.cuda(), lr.cuda(), tok.cuda(), mask.cuda())
+        assert tuple(out.shape) == tuple(ref.shape)
+        assert rel(out, ref) < 2e-2, (size, rel(out, ref))
