@@ -7,11 +7,12 @@
 // buffer: for tap (r,s) the producer asks TMA for the activation box shifted by (r-1, s-1); out-of-image
 // coordinates are filled with zeros by the TMA unit, which is exactly pad_mode='pad', padding=1.
 //
-// Warp roles (256 threads, 1 CTA / SM, persistent over output tiles):
-//   warp 0  : TMA producer (one elected thread)
-//   warp 1  : MMA issuer  (one elected thread)
-//   warp 2  : TMEM allocate / free
-//   warps 4-7: epilogue, thread i of warp w owns accumulator row 32*(w-4)+i (TMEM lane)
+// Warp roles (512 threads, 1 CTA / SM, persistent over output tiles):
+//   warp 0   : TMA producer (one elected thread)
+//   warp 1   : MMA issuer  (one elected thread)
+//   warp 2   : TMEM allocate / free
+//   warps 4-15: epilogue; warp w reads TMEM lane quadrant w % 4 (accumulator rows 32*(w%4) .. +31) and takes
+//              every third column chunk — three warps per scheduler keep the transpose / store chain busy
 #include "common.cuh"
 #include <atomic>
 
@@ -32,6 +33,9 @@ struct TcParams {
   int tn, th, tw;
   int tiles_x, tiles_y;
   int N, n_tiles_n, num_tiles;
+  int m_tiles;
+  int debug;        // MDX_GEMM_DEBUG bit mask (profiling only): 1 = no global stores, 2 = epilogue does nothing
+  int b_resident;   // K fits the B ring: each CTA keeps ONE n-tile's weight slice in smem and streams only A tiles
   void* out;
   long long ldc;
   int out_f32;
@@ -47,15 +51,166 @@ struct TcParams {
 
 template <int BN> struct TcCfg {
   static constexpr int B_STAGE_BYTES = BN * BK * 2;
-  static constexpr int STAGES = (BN >= 256) ? 4 : (BN >= 160 ? 5 : (BN >= 128 ? 5 : 7));
+  static constexpr int STAGES = (BN >= 256) ? 3 : (BN >= 128 ? 5 : 7);
   static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
-  static constexpr int EPI_WARPS = (BN >= 256) ? 4 : 8;      // 4 TMEM lane quadrants x {1,2} column parities
-  static constexpr int THREADS = 128 + 32 * EPI_WARPS;
-  static constexpr int STG_LD = 36;                           // floats per staging row (32 + 4 pad, 16-B aligned)
+  static constexpr int EPI_WARPS = 12;                        // 4 TMEM lane quadrants x 3 column shares
+  static constexpr int THREADS = 128 + 32 * EPI_WARPS;        // 512: one role warpgroup + three epilogue warpgroups
+  static constexpr int STG_BYTES = 3072;                      // per warp: 32 rows x 80 B staging + 512 B bias slice
   static constexpr int STAGING_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 256;
-  static constexpr int SMEM_BYTES = STAGING_OFF + EPI_WARPS * 32 * STG_LD * 4 + 1024 /*align*/;
+  static constexpr int SMEM_BYTES = STAGING_OFF + EPI_WARPS * STG_BYTES + 1024 /*align*/;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
+
+// ------------------------------------------------------------------------------------------------------
+// Epilogue of one 128 x BN accumulator tile for one warp (TMEM lane quadrant in `taddr`, column share cpar of
+// cstep).  tcgen05.ld hands every thread consecutive columns of ITS accumulator row; global memory wants
+// consecutive columns of the SAME row across lanes.  The transpose goes through a per-warp staging tile of
+// 32 rows x 64 payload bytes (80-byte pitch: conflict-free for 16-byte accesses in both directions):
+//   plain bf16 (no residual / per-image bias): 32-column chunks; bias + activation + bf16 packing happen in the
+//     row-owner layout, the coalesced phase is LDS.128 -> STG.128 only;
+//   general (fp32 out and/or residual / per-image bias): 16-column fp32 chunks; the coalesced phase adds bias,
+//     activation and the residual (+ per-image bias), whose loads for chunk c+1 are issued before chunk c is
+//     processed.
+// Either way 4 lanes cover 64 contiguous bytes of one row and a warp instruction covers 8 rows.
+// ------------------------------------------------------------------------------------------------------
+template <bool RES_F32>
+__device__ __forceinline__ float4 epi_load_add(const TcParams& p, long long pix, int col) {
+  float4 acc4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.residual) {
+    if (RES_F32) {
+      acc4 = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + pix * p.ldr + col));
+    } else {
+      const uint2 u = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ldr + col));
+      const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+      acc4 = make_float4(f0.x, f0.y, f1.x, f1.y);
+    }
+  }
+  if (p.rowbias) {
+    const int img = (int)(pix / ((long long)p.H * p.W));
+    const float4 rb = __ldg(reinterpret_cast<const float4*>(p.rowbias + (long long)img * p.ld_rowbias + col));
+    acc4.x += rb.x; acc4.y += rb.y; acc4.z += rb.z; acc4.w += rb.w;
+  }
+  return acc4;
+}
+
+template <int BN, bool OUT_F32, bool HAS_ADD>
+__device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint32_t stg, int lane, int cpar,
+                                         int cstep, int n_tile, long long pix_own) {
+  const int n_out = p.N;
+  const int ocol_tile = n_tile * BN;
+  const int sr8 = lane >> 2, q4 = lane & 3;
+  long long pix8[4];
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) pix8[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 8 + sr8);
+  if constexpr (!OUT_F32 && !HAS_ADD) {
+    constexpr int NCH = BN / 32;
+#pragma unroll 1
+    for (int c = cpar; c < NCH; c += cstep) {
+      const int ocol0 = ocol_tile + c * 32;
+      if (ocol0 >= n_out) break;
+      uint32_t r[32];
+      tmem_ld32(taddr + c * 32, r);
+      float4 b[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        b[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.bias && ocol0 + 4 * j < n_out) b[j] = __ldg(reinterpret_cast<const float4*>(p.bias + ocol0) + j);
+      }
+      tmem_ld_wait();
+      uint32_t pk[16];
+      if (p.act) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          pk[2 * j] = pack_bf16x2(apply_act(__uint_as_float(r[4 * j]) + b[j].x, p.act),
+                                  apply_act(__uint_as_float(r[4 * j + 1]) + b[j].y, p.act));
+          pk[2 * j + 1] = pack_bf16x2(apply_act(__uint_as_float(r[4 * j + 2]) + b[j].z, p.act),
+                                      apply_act(__uint_as_float(r[4 * j + 3]) + b[j].w, p.act));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          pk[2 * j] = pack_bf16x2(__uint_as_float(r[4 * j]) + b[j].x, __uint_as_float(r[4 * j + 1]) + b[j].y);
+          pk[2 * j + 1] = pack_bf16x2(__uint_as_float(r[4 * j + 2]) + b[j].z, __uint_as_float(r[4 * j + 3]) + b[j].w);
+        }
+      }
+      __syncwarp();  // the previous chunk's coalesced reads of the staging tile are done
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sts128(stg + lane * 80 + 16 * j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      __syncwarp();
+      const bool cok = ocol0 + q4 * 8 < n_out;
+      bf16* obase = reinterpret_cast<bf16*>(p.out) + ocol0 + q4 * 8;
+#pragma unroll
+      for (int pass = 0; pass < 4; ++pass) {
+        const uint4 u = lds128(stg + (pass * 8 + sr8) * 80 + q4 * 16);
+        const long long pix = pix8[pass];
+        if (cok && pix >= 0 && !(p.debug & 1)) *reinterpret_cast<uint4*>(obase + pix * p.ldc) = u;
+      }
+    }
+  } else {
+    constexpr int NCH = BN / 16;
+    float4 radd[4];
+    if constexpr (HAS_ADD) {   // residual (+ per-image bias) of this warp's first chunk
+      const int col = ocol_tile + cpar * 16 + q4 * 4;
+#pragma unroll
+      for (int pass = 0; pass < 4; ++pass) {
+        radd[pass] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (cpar < NCH && col < n_out && pix8[pass] >= 0)
+          radd[pass] = p.res_f32 ? epi_load_add<true>(p, pix8[pass], col) : epi_load_add<false>(p, pix8[pass], col);
+      }
+    }
+#pragma unroll 1
+    for (int c = cpar; c < NCH; c += cstep) {
+      const int ocol0 = ocol_tile + c * 16;
+      if (ocol0 >= n_out) break;
+      const int col = ocol0 + q4 * 4;
+      const bool col_ok = col < n_out;
+      uint32_t r[16];
+      tmem_ld16(taddr + c * 16, r);
+      float4 rnext[4];
+      if constexpr (HAS_ADD) {   // next chunk's loads fly while this chunk is transposed and stored
+        const int coln = col + cstep * 16;
+        const bool nok = (c + cstep) < NCH && coln < n_out;
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) {
+          rnext[pass] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (nok && pix8[pass] >= 0)
+            rnext[pass] = p.res_f32 ? epi_load_add<true>(p, pix8[pass], coln) : epi_load_add<false>(p, pix8[pass], coln);
+        }
+      }
+      float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (col_ok && p.bias) bz = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+      tmem_ld_wait();
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sts128(stg + lane * 80 + 16 * j, r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+      __syncwarp();
+#pragma unroll
+      for (int pass = 0; pass < 4; ++pass) {
+        const uint4 u = lds128(stg + (pass * 8 + sr8) * 80 + q4 * 16);
+        float4 o = make_float4(__uint_as_float(u.x) + bz.x, __uint_as_float(u.y) + bz.y, __uint_as_float(u.z) + bz.z,
+                               __uint_as_float(u.w) + bz.w);
+        if (p.act) {  // activation sits between the bias and the residual
+          o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act);
+        }
+        if constexpr (HAS_ADD) { o.x += radd[pass].x; o.y += radd[pass].y; o.z += radd[pass].z; o.w += radd[pass].w; }
+        const long long pix = pix8[pass];
+        if (!col_ok || pix < 0 || (p.debug & 1)) continue;
+        if constexpr (OUT_F32) {
+          *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + col) = o;
+        } else {
+          uint2 w;
+          w.x = pack_bf16x2(o.x, o.y);
+          w.y = pack_bf16x2(o.z, o.w);
+          *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + col) = w;
+        }
+      }
+      if constexpr (HAS_ADD) {
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) radd[pass] = rnext[pass];
+      }
+    }
+  }
+}
 
 template <int BN>
 __global__ void __launch_bounds__(TcCfg<BN>::THREADS, 1)
@@ -72,7 +227,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* bfull = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -92,6 +248,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], 32 * Cfg::EPI_WARPS);
     }
+    mbar_init(bfull, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -104,15 +261,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
 
   const int tiles_per_img_grid = p.tiles_x * p.tiles_y;
+  // Tile schedule.  Streaming mode: tiles round-robin over CTAs, n fastest (CTAs that run together share the A tile
+  // in L2).  Resident mode (small K): CTA b owns n-tile b % n_tiles_n for its whole life and walks m-tiles, so the
+  // weight slice is fetched once per CTA instead of once per tile.
+  const int cta_per_n = p.b_resident ? (int)gridDim.x / p.n_tiles_n : 1;
+  auto tile_at = [&](int it, int& m_tile, int& n_tile) -> bool {
+    if (p.b_resident) {
+      n_tile = (int)blockIdx.x % p.n_tiles_n;
+      m_tile = (int)blockIdx.x / p.n_tiles_n + it * cta_per_n;
+      return m_tile < p.m_tiles;
+    }
+    const long long tile = (long long)blockIdx.x + (long long)it * gridDim.x;
+    if (tile >= p.num_tiles) return false;
+    n_tile = (int)(tile % p.n_tiles_n);
+    m_tile = (int)(tile / p.n_tiles_n);
+    return true;
+  };
 
+  // Register rebalancing (512 threads start at 128 registers each): the role warpgroup keeps 40, the three epilogue
+  // warpgroups take 152 (128 x 40 + 384 x 152 = 63488 <= 65536).  Each setmaxnreg sits at the top of its own branch.
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
   if (warp == 0) {
     if (elect_one()) {
       // ===================== TMA producer =====================
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles_n;
-        const int m_tile = tile / p.n_tiles_n;
+      int m_tile, n_tile;
+      if (p.b_resident && tile_at(0, m_tile, n_tile)) {
+        mbar_arrive_expect_tx(bfull, p.total_kb * Cfg::B_STAGE_BYTES);
+        for (int kb = 0; kb < p.total_kb; ++kb)
+          tma_load_2d(sB + kb * Cfg::B_STAGE_BYTES, &tmB, bfull, kb * BK, n_tile * BN);
+      }
+      const uint32_t stage_tx = p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + Cfg::B_STAGE_BYTES;
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
         const int x0 = (m_tile % p.tiles_x) * p.tw;
         const int y0 = ((m_tile / p.tiles_x) % p.tiles_y) * p.th;
         const int n0 = (m_tile / tiles_per_img_grid) * p.tn;
@@ -126,9 +308,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const int dx = taps == 9 ? tap % 3 - 1 : 0;
             for (int cb = 0; cb < nkb; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
-              mbar_arrive_expect_tx(&full[stage], A_STAGE_BYTES + Cfg::B_STAGE_BYTES);
+              mbar_arrive_expect_tx(&full[stage], stage_tx);
               tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 + dx, y0 + dy, n0);
-              tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
+              if (!p.b_resident) tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
               kcoord += BK;
               if (++stage == STAGES) {
                 stage = 0;
@@ -146,9 +328,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       int stage = 0;
       uint32_t phase = 0;
       uint32_t iter = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++iter) {
+      int m_tile, n_tile;
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
         const uint32_t as = iter & 1;
         const uint32_t aph = (iter >> 1) & 1;
+        if (p.b_resident && it == 0) mbar_wait(bfull, 0);
         mbar_wait(&tempty[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
@@ -156,7 +340,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sA + stage * A_STAGE_BYTES);
-          const uint32_t b_base = smem_u32(sB + stage * Cfg::B_STAGE_BYTES);
+          const uint32_t b_base = smem_u32(sB + (p.b_resident ? kb : stage) * Cfg::B_STAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             umma_bf16(d_tmem, umma_desc_sw128(a_base + k * 32), umma_desc_sw128(b_base + k * 32), idesc,
@@ -171,31 +355,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         }
       }
     }
-  } else if (warp >= 4) {
-    // ===================== epilogue =====================
-    // Phase 1 (row-owner layout, what tcgen05.ld gives): thread `lane` of the warp holds accumulator row
-    //   32*q + lane; GEGLU's value*gelu(gate) is formed here.  The chunk (<= 32 output columns) goes to a
-    //   per-warp smem staging tile.
-    // Phase 2 (coalesced layout): 8 lanes cover 32 consecutive columns of one row, 4 rows per pass, so global
-    //   reads of the residual and writes of the output are contiguous 128-byte (fp32) / 64-byte (bf16) segments.
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 152;");
+    // ===================== epilogue (see epi_tile) =====================
     constexpr int NEW = Cfg::EPI_WARPS;
     const int ew = warp - 4;
     const int qw = ew & 3;                 // TMEM lane quadrant this warp may read
-    const int cpar = ew >> 2;              // with 8 epilogue warps: even / odd chunks
+    const int cpar = ew >> 2;              // column share 0..2 of this warp inside its quadrant
     const int row = qw * 32 + lane;
     const int xl = row % p.tw;
     const int yl = (row / p.tw) % p.th;
     const int nl = row / (p.tw * p.th);
-    float* stg = reinterpret_cast<float*>(smem + Cfg::STAGING_OFF) + ew * (32 * Cfg::STG_LD);
-    const int sub_row = lane >> 3;         // phase 2: row within a pass of 4
-    const int c4 = (lane & 7) * 4;         // phase 2: first of this lane's 4 columns inside the chunk
-    constexpr int OUTW = BN;               // output columns per tile (GEGLU: BN/2)
+    const uint32_t stg = smem_u32(smem + Cfg::STAGING_OFF) + ew * Cfg::STG_BYTES;
+    const bool has_add = p.residual != nullptr || p.rowbias != nullptr;
     uint32_t iter = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++iter) {
+    int m_tile, n_tile;
+    for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
       const uint32_t as = iter & 1;
       const uint32_t aph = (iter >> 1) & 1;
-      const int n_tile = tile % p.n_tiles_n;
-      const int m_tile = tile / p.n_tiles_n;
       const int x = (m_tile % p.tiles_x) * p.tw + xl;
       const int y = ((m_tile / p.tiles_x) % p.tiles_y) * p.th + yl;
       const int n = (m_tile / tiles_per_img_grid) * p.tn + nl;
@@ -206,162 +384,81 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + as * BN;
 
-      // pixel index of the row each lane serves in each phase-2 pass (constant over the tile's chunks)
-      long long pixs[8];
-#pragma unroll
-      for (int pass = 0; pass < 8; ++pass) pixs[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 4 + sub_row);
-
-      const int outw = p.geglu ? OUTW / 2 : OUTW;            // output columns this tile produces
-      const int n_out = p.geglu ? p.N / 2 : p.N;             // output columns of the whole GEMM
-      const int ocol_tile = n_tile * outw;
-      if (p.geglu) {
-        // GEGLU: per sub-chunk of 16 output columns stage [value16 | gate16], then in the coalesced layout
-        // (4 lanes x 4 columns per row, 8 rows per pass) form (value + bv) * gelu(gate + bg) and store bf16/fp32.
+      if (p.debug & 2) {
+        // profiling only: drop the tile
+      } else if (p.geglu) {
+        // GEGLU: the tile holds [BN/2 value columns | the matching BN/2 gate columns].  In the row-owner layout a
+        // thread forms (value + bv) * gelu(gate + bg) for up to 32 output columns of its row, packs bf16, and the
+        // unit goes through the 80-byte-row staging tile to 16-byte coalesced stores (as the plain bf16 path).
         constexpr int HALF = BN / 2;
-        const int sr8 = lane >> 2, c4g = (lane & 3) * 4;
+        constexpr int NU = (HALF + 31) / 32;           // units of 32 output columns (the last one may hold 16)
+        const int n_out = p.N / 2;
+        const int ocol_tile = n_tile * HALF;
+        const int sr8 = lane >> 2, q4 = lane & 3;
         long long pix8[4];
 #pragma unroll
         for (int pass = 0; pass < 4; ++pass) pix8[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 8 + sr8);
 #pragma unroll 1
-        for (int sc = cpar; sc < HALF / 16; sc += (NEW / 4)) {
-          const int ocol0 = ocol_tile + sc * 16;
+        for (int u = cpar; u < NU; u += (NEW / 4)) {
+          const int ucol = u * 32;
+          const int uw = (HALF - ucol) < 32 ? (HALF - ucol) : 32;       // 32 or 16
+          const int ocol0 = ocol_tile + ucol;
           if (ocol0 >= n_out) break;
-          uint32_t rv[16], rg[16];
-          tmem_ld16(taddr + sc * 16, rv);
-          tmem_ld16(taddr + HALF + sc * 16, rg);
-          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f), bg = bv;
-          if (p.bias) {  // bias is packed like the weight rows: [value half | gate half] per tile
-            bv = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * BN + sc * 16 + c4g));
-            bg = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile * BN + HALF + sc * 16 + c4g));
+          const float* bvp = p.bias + n_tile * BN + ucol;   // bias is packed like the weight rows
+          float blv = 0.f, blg = 0.f;                       // lane <-> column; broadcast through smem below
+          if (p.bias && lane < uw) {
+            blv = __ldg(bvp + lane);
+            blg = __ldg(bvp + HALF + lane);
           }
+          uint32_t rv[32], rg[32];
+          if (uw == 32) {
+            tmem_ld32(taddr + ucol, rv);
+            tmem_ld32(taddr + HALF + ucol, rg);
+          } else {
+            tmem_ld16(taddr + ucol, *reinterpret_cast<uint32_t(*)[16]>(&rv[0]));
+            tmem_ld16(taddr + HALF + ucol, *reinterpret_cast<uint32_t(*)[16]>(&rg[0]));
+          }
+          __syncwarp();  // the previous unit's reads of the staging tile and the bias slice are done
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(stg + 2560 + lane * 4), "r"(__float_as_uint(blv)) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(stg + 2688 + lane * 4), "r"(__float_as_uint(blg)) : "memory");
+          __syncwarp();
           tmem_ld_wait();
-          __syncwarp();
+          uint32_t pk[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            *reinterpret_cast<uint4*>(stg + lane * Cfg::STG_LD + 4 * j) = make_uint4(rv[4 * j], rv[4 * j + 1], rv[4 * j + 2], rv[4 * j + 3]);
-            *reinterpret_cast<uint4*>(stg + lane * Cfg::STG_LD + 16 + 4 * j) = make_uint4(rg[4 * j], rg[4 * j + 1], rg[4 * j + 2], rg[4 * j + 3]);
+          for (int j = 0; j < 8; ++j) {
+            if (4 * j < uw) {
+              const uint4 ubv = lds128(stg + 2560 + 16 * j), ubg = lds128(stg + 2688 + 16 * j);
+              const float4 bv = make_float4(__uint_as_float(ubv.x), __uint_as_float(ubv.y), __uint_as_float(ubv.z), __uint_as_float(ubv.w));
+              const float4 bg = make_float4(__uint_as_float(ubg.x), __uint_as_float(ubg.y), __uint_as_float(ubg.z), __uint_as_float(ubg.w));
+              const float o0 = (__uint_as_float(rv[4 * j]) + bv.x) * gelu_tanh_fast(__uint_as_float(rg[4 * j]) + bg.x);
+              const float o1 = (__uint_as_float(rv[4 * j + 1]) + bv.y) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 1]) + bg.y);
+              const float o2 = (__uint_as_float(rv[4 * j + 2]) + bv.z) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 2]) + bg.z);
+              const float o3 = (__uint_as_float(rv[4 * j + 3]) + bv.w) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 3]) + bg.w);
+              pk[2 * j] = pack_bf16x2(o0, o1);
+              pk[2 * j + 1] = pack_bf16x2(o2, o3);
+            } else {
+              pk[2 * j] = 0u;
+              pk[2 * j + 1] = 0u;
+            }
           }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) sts128(stg + lane * 80 + 16 * j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
           __syncwarp();
+          const bool cok = q4 * 8 < uw && ocol0 + q4 * 8 < n_out;
+          bf16* obase = reinterpret_cast<bf16*>(p.out) + ocol0 + q4 * 8;
 #pragma unroll
           for (int pass = 0; pass < 4; ++pass) {
-            const int r = pass * 8 + sr8;
+            const uint4 w = lds128(stg + (pass * 8 + sr8) * 80 + q4 * 16);
             const long long pix = pix8[pass];
-            if (pix < 0) continue;
-            const float4 a = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + c4g);
-            const float4 g = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + 16 + c4g);
-            float4 o;
-            o.x = (a.x + bv.x) * gelu_tanh_fast(g.x + bg.x);
-            o.y = (a.y + bv.y) * gelu_tanh_fast(g.y + bg.y);
-            o.z = (a.z + bv.z) * gelu_tanh_fast(g.z + bg.z);
-            o.w = (a.w + bv.w) * gelu_tanh_fast(g.w + bg.w);
-            if (p.out_f32) {
-              *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0 + c4g) = o;
-            } else {
-              uint2 u;
-              u.x = pack_bf16x2(o.x, o.y);
-              u.y = pack_bf16x2(o.z, o.w);
-              *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + ocol0 + c4g) = u;
-            }
+            if (cok && pix >= 0 && !(p.debug & 1)) *reinterpret_cast<uint4*>(obase + pix * p.ldc) = w;
           }
         }
-        tc_fence_before();
-        mbar_arrive(&tempty[as]);
-        continue;
-      }
-      const int nchunks = (outw + 31) / 32;
-#pragma unroll 1
-      for (int c = cpar; c < nchunks; c += (NEW / 4)) {
-        const int cw = min(32, outw - c * 32);               // 32 or 16
-        const int ocol0 = ocol_tile + c * 32;
-        if (ocol0 >= n_out) break;
-        // ---- prefetch (coalesced layout): everything phase 2 adds that does not depend on the accumulator.
-        // Issued before the TMEM load so that the 8 x 512 B reads per warp are in flight together. ----
-        const bool col_ok = c4 < cw && (ocol0 + c4) < n_out;
-        float4 radd[8];
-#pragma unroll
-        for (int pass = 0; pass < 8; ++pass) {
-          float4 acc4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          const long long pix = pixs[pass];
-          if (col_ok && pix >= 0) {
-            if (p.residual) {
-              if (p.res_f32) {
-                acc4 = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + pix * p.ldr + ocol0 + c4));
-              } else {
-                const uint2 u = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ldr + ocol0 + c4));
-                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
-                acc4 = make_float4(f0.x, f0.y, f1.x, f1.y);
-              }
-            }
-            if (p.rowbias) {
-              const int img = (int)(pix / ((long long)p.H * p.W));
-              const float4 rb = __ldg(reinterpret_cast<const float4*>(p.rowbias + (long long)img * p.ld_rowbias + ocol0 + c4));
-              acc4.x += rb.x; acc4.y += rb.y; acc4.z += rb.z; acc4.w += rb.w;
-            }
-          }
-          radd[pass] = acc4;
-        }
-        // ---- phase 1 ----
-        float v[32];
-        if (!p.geglu) {
-          uint32_t r0[16], r1[16];
-          tmem_ld16(taddr + c * 32, r0);
-          if (cw > 16) tmem_ld16(taddr + c * 32 + 16, r1);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) { v[i] = __uint_as_float(r0[i]); v[16 + i] = cw > 16 ? __uint_as_float(r1[i]) : 0.f; }
-        } else {
-          constexpr int HALF = BN / 2;
-#pragma unroll
-          for (int hsel = 0; hsel < 2; ++hsel) {
-            if (hsel * 16 < cw) {
-              uint32_t rv[16], rg[16];
-              tmem_ld16(taddr + c * 32 + hsel * 16, rv);
-              tmem_ld16(taddr + HALF + c * 32 + hsel * 16, rg);
-              tmem_ld_wait();
-              const int bcol_v = n_tile * BN + c * 32 + hsel * 16;   // bias is packed like the weight rows
-              const int bcol_g = bcol_v + HALF;
-#pragma unroll
-              for (int i = 0; i < 16; ++i) {
-                float a = __uint_as_float(rv[i]);
-                float g = __uint_as_float(rg[i]);
-                if (p.bias) { a += __ldg(p.bias + bcol_v + i); g += __ldg(p.bias + bcol_g + i); }
-                v[hsel * 16 + i] = a * gelu_tanh_fast(g);
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 16; ++i) v[hsel * 16 + i] = 0.f;
-            }
-          }
-        }
-        __syncwarp();  // previous chunk's phase-2 reads of the staging tile are done
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(stg + lane * Cfg::STG_LD + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        __syncwarp();
-        // ---- phase 2 ----
-        float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (col_ok && p.bias && !p.geglu) bz = __ldg(reinterpret_cast<const float4*>(p.bias + ocol0 + c4));
-#pragma unroll
-        for (int pass = 0; pass < 8; ++pass) {
-          const int r = pass * 4 + sub_row;
-          const long long pix = pixs[pass];
-          if (!col_ok || pix < 0) continue;
-          float4 o = *reinterpret_cast<const float4*>(stg + r * Cfg::STG_LD + c4);
-          if (p.act) {  // activation sits between the bias and the residual (radd carries rowbias + residual)
-            o.x = apply_act(o.x + bz.x, p.act) + radd[pass].x; o.y = apply_act(o.y + bz.y, p.act) + radd[pass].y;
-            o.z = apply_act(o.z + bz.z, p.act) + radd[pass].z; o.w = apply_act(o.w + bz.w, p.act) + radd[pass].w;
-          } else {
-            o.x += bz.x + radd[pass].x; o.y += bz.y + radd[pass].y; o.z += bz.z + radd[pass].z; o.w += bz.w + radd[pass].w;
-          }
-          if (p.out_f32) {
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.ldc + ocol0 + c4) = o;
-          } else {
-            uint2 u;
-            u.x = pack_bf16x2(o.x, o.y);
-            u.y = pack_bf16x2(o.z, o.w);
-            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + ocol0 + c4) = u;
-          }
-        }
+      } else if (p.out_f32) {
+        if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
+        else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
+      } else {
+        if (has_add) epi_tile<BN, false, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
+        else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
       }
       tc_fence_before();
       mbar_arrive(&tempty[as]);
@@ -475,7 +572,16 @@ int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p,
     attr_set = true;
   }
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  gemm_tc_kernel<BN><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, p);
+  TcParams q = p;
+  if (const char* dbg = getenv("MDX_GEMM_DEBUG")) q.debug = atoi(dbg);
+  const bool no_resident = getenv("MDX_GEMM_NO_RESIDENT") != nullptr;  // A/B switch for tests and profiling
+  // weights stay in smem when the whole K fits the B ring and every CTA would otherwise re-fetch them >= 3 times
+  if (!no_resident && p.nseg == 1 && p.seg_taps[0] == 1 && p.total_kb <= TcCfg<BN>::STAGES &&
+      p.n_tiles_n <= num_sms() && (long long)p.m_tiles * p.n_tiles_n >= 3ll * num_sms()) {
+    q.b_resident = 1;
+    grid = (num_sms() / p.n_tiles_n) * p.n_tiles_n;
+  }
+  gemm_tc_kernel<BN><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;
@@ -528,7 +634,9 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   if (a->rowbias)
     MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->rowbias) & 15) == 0 && a->ld_rowbias % 4 == 0,
                   "mdx_gemm_tc: rowbias alignment");
-  if (a->geglu) MDX_CHECK_ARG(!a->rowbias && !a->residual && !a->act && a->N % 32 == 0, "mdx_gemm_tc: geglu excludes rowbias/residual/act");
+  if (a->geglu)
+    MDX_CHECK_ARG(!a->rowbias && !a->residual && !a->act && a->N % 32 == 0 && a->out_dtype == MDX_BF16,
+                  "mdx_gemm_tc: geglu excludes rowbias/residual/act and writes bf16");
   MDX_CHECK_ARG(a->act >= 0 && a->act <= 2, "mdx_gemm_tc: act must be 0, 1 (gelu) or 2 (quick gelu)");
   if (a->act) MDX_CHECK_ARG(!a->rowbias, "mdx_gemm_tc: act excludes rowbias");
 
@@ -562,6 +670,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   long long nt = (long long)p.tiles_x * p.tiles_y * tiles_n * p.n_tiles_n;
   MDX_CHECK_ARG(nt < (1ll << 31), "mdx_gemm_tc: too many tiles");
   p.num_tiles = (int)nt;
+  p.m_tiles = p.tiles_x * p.tiles_y * tiles_n;
   p.out = a->out; p.ldc = a->ldc; p.out_f32 = a->out_dtype == MDX_F32;
   p.bias = a->bias; p.rowbias = a->rowbias; p.ld_rowbias = a->ld_rowbias;
   p.residual = a->residual; p.ldr = a->ldr; p.res_f32 = a->residual_dtype == MDX_F32;

@@ -73,3 +73,41 @@ def test_embedding():
     ref = (table[ids.long()] + pos[None]).reshape(-1, 64)
     out = ops.embedding(table.cuda(), pos.cuda(), ids.cuda())
     assert torch.equal(out.cpu(), ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,K,N,geglu", [(128 * 450 + 37, 320, 320, False), (128 * 230, 320, 960, False),
+                                          (128 * 120, 192, 640, False), (128 * 60, 320, 2560, True),
+                                          (128 * 500, 64, 128, False)])
+def test_gemm_tc_resident_weights(M, K, N, geglu):
+    """Small-K GEMMs keep one n-tile's weight slice in shared memory for the CTA's lifetime (gemm_tc.cu, resident
+    mode).  Same inputs through the streaming schedule (MDX_GEMM_NO_RESIDENT=1) must give identical bits, and both
+    must match torch."""
+    import os
+    from minddiffusion_b200 import ops
+    from minddiffusion_b200.unet import pack_geglu
+    g = torch.Generator().manual_seed(M % 1000 + K + N)
+    a = torch.randn(M, K, generator=g).bfloat16()
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, generator=g)
+    res = torch.randn(M, N // 2 if geglu else N, generator=g)
+    if geglu:
+        val, gate = (a.float() @ w.float().t() + bias).chunk(2, dim=1)
+        ref = val * torch.nn.functional.gelu(gate, approximate="tanh")
+        wp, bp, bn = pack_geglu(w.cuda(), bias.cuda())
+        run = lambda: ops.gemm_tc([(a.cuda(), 1)], wp, bias=bp, geglu=True, block_n=bn)
+        tol = 2e-2
+    else:
+        ref = a.float() @ w.float().t() + bias + res
+        run = lambda: ops.gemm_tc([(a.cuda(), 1)], w.cuda(), bias=bias.cuda(), residual=res.cuda(),
+                                  out_dtype=torch.float32)
+        tol = 1e-4
+    out = run()
+    os.environ["MDX_GEMM_NO_RESIDENT"] = "1"
+    try:
+        out_stream = run()
+    finally:
+        del os.environ["MDX_GEMM_NO_RESIDENT"]
+    assert torch.equal(out, out_stream)
+    err = float((out.float().cpu() - ref).abs().max() / ref.abs().max())
+    assert err < tol, err
