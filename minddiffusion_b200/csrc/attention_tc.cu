@@ -5,9 +5,9 @@
 // One CTA = 128 queries of one (batch, head); keys/values stream through in tiles of 128.
 //   warp 0 : TMA producer   Q once, then K and V tiles (3-D boxes cut straight out of the fused [B, N, 3C] / [B, L, 2C]
 //                           projection buffers, 128-byte swizzle), two mbarrier rings
-//   warp 1 : MMA issuer     S_j = Q K_j^T   (M128 x N128 x K64, both operands K-major)        -> TMEM S[j&1]
+//   warp 1 : MMA issuer     S_j = Q K_j^T   (M128 x N128 x K64, both operands K-major)        -> TMEM S[j%3]
 //                           O_j = P_j V_j   (M128 x N64 x K128, A = P from smem, B = V MN-major) -> TMEM O[j&1]
-//   warp 2 : TMEM allocate / free (512 columns: 2 x 128 for S, 2 x 64 for O)
+//   warp 2 : TMEM allocate / free (512 columns: 3 x 128 for S, 2 x 64 for O)
 //   warps 4-11: softmax, two warpgroups ping-ponging over key tiles (group g owns tiles g, g+2, ...).  Thread =
 //                           query row (TMEM lane), so row max / row sum need no shuffles.  Two passes over S in TMEM
 //                           (max, then exp2 + sum), P written as bf16 into a 128B-swizzled smem operand, running
@@ -24,8 +24,9 @@ namespace {
 constexpr int AT_BM = 128;   // queries per CTA
 constexpr int AT_BN = 128;   // keys per tile
 constexpr int AT_D = 64;
-constexpr int AT_KS = 3;     // K ring depth
-constexpr int AT_VS = 3;     // V ring depth
+constexpr int AT_KS = 4;     // K ring depth
+constexpr int AT_VS = 4;     // V ring depth
+constexpr int AT_SS = 3;     // S accumulators in TMEM: Q K^T runs two tiles ahead of the softmax
 constexpr int TILE_BYTES = 128 * 64 * 2;  // 16 KiB: one [128 x 64] bf16 operand block
 
 struct AttnTcP {
@@ -77,9 +78,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* k_empty = k_full + AT_KS;      // AT_KS
   uint64_t* v_full = k_empty + AT_KS;      // AT_VS
   uint64_t* v_empty = v_full + AT_VS;      // AT_VS
-  uint64_t* s_full = v_empty + AT_VS;      // 2
-  uint64_t* s_empty = s_full + 2;          // 2
-  uint64_t* p_full = s_empty + 2;          // 2
+  uint64_t* s_full = v_empty + AT_VS;      // AT_SS
+  uint64_t* s_empty = s_full + AT_SS;      // AT_SS
+  uint64_t* p_full = s_empty + AT_SS;      // 2
   uint64_t* p_empty = p_full + 2;          // 2
   uint64_t* o_full = p_empty + 2;          // 2
   uint64_t* o_empty = o_full + 2;          // 2
@@ -99,8 +100,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     mbar_init(q_full, 1);
     for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
     for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 128); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1);  mbar_init(&s_empty[i], 128);
       mbar_init(&p_full[i], 128); mbar_init(&p_empty[i], 1);
       mbar_init(&o_full[i], 1);  mbar_init(&o_empty[i], 128);
     }
@@ -114,8 +115,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t TM_S = tmem_base;          // S[sb] at columns sb*128
-  const uint32_t TM_O = tmem_base + 256;    // O[ob] at columns 256 + ob*64
+  const uint32_t TM_S = tmem_base;                    // S[sb] at columns sb*128, sb = tile % 3
+  const uint32_t TM_O = tmem_base + AT_SS * AT_BN;    // O[ob] at columns 384 + ob*64
 
   // Register rebalancing: the producer / MMA / allocator warpgroup needs few registers, the softmax warpgroups hold a
   // whole score row (128) plus the running output row (64) each.  384 threads x 168 = 128 x 40 + 256 x 232.
@@ -164,10 +165,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         umma_commit(&p_empty[pb]);
       };
       mbar_wait(q_full, 0);
+      // issue order S0 S1 S2 PV0 S3 PV1 ...: S_j only needs the softmax of tile j-3 to have drained its buffer, so
+      // the scores of a group's next tile are complete before the group finishes its current one
       for (int j = 0; j < T; ++j) {
-        const int ks = j % AT_KS, sb = j & 1;
+        const int ks = j % AT_KS, sb = j % AT_SS;
         mbar_wait(&k_full[ks], (j / AT_KS) & 1);
-        mbar_wait(&s_empty[sb], ((j >> 1) & 1) ^ 1);
+        mbar_wait(&s_empty[sb], ((j / AT_SS) & 1) ^ 1);
         tc_fence_after();
         const uint32_t k_base = smem_u32(smem + OFF_K + ks * TILE_BYTES);
 #pragma unroll
@@ -176,8 +179,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     k != 0 ? 1u : 0u);
         umma_commit(&s_full[sb]);
         umma_commit(&k_empty[ks]);
-        if (j >= 1) issue_pv(j - 1);
+        if (j >= 2) issue_pv(j - 2);
       }
+      if (T >= 2) issue_pv(T - 2);
       issue_pv(T - 1);
     }
   }
@@ -198,13 +202,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const float c = p.sl2;
     uint8_t* prow = smem + OFF_P + g * 2 * TILE_BYTES + row * 128;
     const int swz = row & 7;
-    const uint32_t ts = TM_S + lane_off + g * AT_BN;
     const uint32_t to = TM_O + lane_off + g * AT_D;
 
     int it = 0;  // this group's iteration count (phase bit of its barriers)
     for (int j = g; j < T; j += 2, ++it) {
-      mbar_wait(&s_full[g], it & 1);
+      const int sb = j % AT_SS;
+      mbar_wait(&s_full[sb], (j / AT_SS) & 1);
       tc_fence_after();
+      const uint32_t ts = TM_S + lane_off + sb * AT_BN;
       const int key0 = j * AT_BN;
       // ---- one pass over S: all 128 scores of the row into registers (4 TMEM loads in flight, one wait) ----
       uint32_t sr[AT_BN];
@@ -251,7 +256,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       tc_fence_before();
       fence_proxy_async_smem();          // generic-proxy stores of P -> visible to the tensor core (async proxy)
       mbar_arrive(&p_full[g]);
-      mbar_arrive(&s_empty[g]);
+      mbar_arrive(&s_empty[sb]);
       // ---- deferred accumulation of this group's previous tile: O <- (O + O_prev) * alpha ----
       if (it >= 1) {
         mbar_wait(&o_full[g], (it - 1) & 1);
