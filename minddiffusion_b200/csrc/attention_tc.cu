@@ -24,8 +24,9 @@ namespace {
 constexpr int AT_BM = 128;   // queries per CTA
 constexpr int AT_BN = 128;   // keys per tile
 constexpr int AT_D = 64;
-constexpr int AT_KS = 4;     // K ring depth
-constexpr int AT_VS = 4;     // V ring depth
+constexpr int AT_KS = 3;     // K ring depth
+constexpr int AT_VS = 3;     // V ring depth
+constexpr int AT_PS = 3;     // P operand buffers (tile % 3): never waits for the P V product of the tile before
 constexpr int AT_SS = 3;     // S accumulators in TMEM: Q K^T runs two tiles ahead of the softmax
 constexpr int TILE_BYTES = 128 * 64 * 2;  // 16 KiB: one [128 x 64] bf16 operand block
 
@@ -40,8 +41,8 @@ struct AttnTcP {
 constexpr int OFF_Q = 0;
 constexpr int OFF_K = OFF_Q + TILE_BYTES;
 constexpr int OFF_V = OFF_K + AT_KS * TILE_BYTES;
-constexpr int OFF_P = OFF_V + AT_VS * TILE_BYTES;          // 2 buffers x 2 K-blocks
-constexpr int OFF_BAR = OFF_P + 2 * 2 * TILE_BYTES;
+constexpr int OFF_P = OFF_V + AT_VS * TILE_BYTES;          // AT_PS buffers x 2 K-blocks
+constexpr int OFF_BAR = OFF_P + AT_PS * 2 * TILE_BYTES;
 constexpr int OFF_XML = OFF_BAR + 512;
 constexpr int AT_SMEM = OFF_XML + 1024 + 1024;
 
@@ -55,6 +56,25 @@ __device__ __forceinline__ float max3f(float a, float b, float c) {
   float r;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
   return r;
+}
+// packed fp32 pairs (sm_100 FFMA2 / FADD2): one issue slot for two lanes of the softmax's scale-subtract and row sum
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\tmov.b64 rc, {%5, %5};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+__device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1) {
+  asm("{\n\t.reg .b64 ra, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rd, {%0, %1};\n\tadd.rn.f32x2 rd, rd, ra;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "+f"(d0), "+f"(d1)
+      : "f"(a0), "f"(a1));
+}
+__device__ __forceinline__ void fmul2(float& d0, float& d1, float b) {
+  asm("{\n\t.reg .b64 rb, rd;\n\tmov.b64 rb, {%2, %2};\n\tmov.b64 rd, {%0, %1};\n\tmul.rn.f32x2 rd, rd, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "+f"(d0), "+f"(d1)
+      : "f"(b));
 }
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -80,9 +100,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* v_empty = v_full + AT_VS;      // AT_VS
   uint64_t* s_full = v_empty + AT_VS;      // AT_SS
   uint64_t* s_empty = s_full + AT_SS;      // AT_SS
-  uint64_t* p_full = s_empty + AT_SS;      // 2
-  uint64_t* p_empty = p_full + 2;          // 2
-  uint64_t* o_full = p_empty + 2;          // 2
+  uint64_t* p_full = s_empty + AT_SS;      // AT_PS
+  uint64_t* p_empty = p_full + AT_PS;      // AT_PS
+  uint64_t* o_full = p_empty + AT_PS;      // 2
   uint64_t* o_empty = o_full + 2;          // 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
 
@@ -101,10 +121,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
     for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 128); }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&p_full[i], 128); mbar_init(&p_empty[i], 1);
-      mbar_init(&o_full[i], 1);  mbar_init(&o_empty[i], 128);
-    }
+    for (int i = 0; i < AT_PS; ++i) { mbar_init(&p_full[i], 128); mbar_init(&p_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -147,8 +165,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
       const uint32_t q_base = smem_u32(smem + OFF_Q);
       auto issue_pv = [&](int i) {
-        const int pb = i & 1, vs = i % AT_VS, ob = i & 1;
-        mbar_wait(&p_full[pb], (i >> 1) & 1);
+        const int pb = i % AT_PS, vs = i % AT_VS, ob = i & 1;
+        mbar_wait(&p_full[pb], (i / AT_PS) & 1);
         mbar_wait(&v_full[vs], (i / AT_VS) & 1);
         mbar_wait(&o_empty[ob], ((i >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -200,7 +218,6 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int i = 0; i < AT_D; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
     const float c = p.sl2;
-    uint8_t* prow = smem + OFF_P + g * 2 * TILE_BYTES + row * 128;
     const int swz = row & 7;
     const uint32_t to = TM_O + lane_off + g * AT_D;
 
@@ -235,27 +252,32 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       const float alpha = ex2_approx((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
       const float msc = m_new * c;
       // ---- p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
-      mbar_wait(&p_empty[g], (it & 1) ^ 1);
-      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+      const int pb = j % AT_PS;
+      uint8_t* prow = smem + OFF_P + pb * 2 * TILE_BYTES + row * 128;
+      mbar_wait(&p_empty[pb], ((j / AT_PS) & 1) ^ 1);
+      float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const float nmsc = -msc;
 #pragma unroll
       for (int ch = 0; ch < AT_BN / 8; ++ch) {                // 16 chunks of 8 keys (16 B each)
         uint32_t pk[4];
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
           const int i = ch * 8 + h * 2;
-          const float p0 = ex2_approx(fmaf(__uint_as_float(sr[i]), c, -msc));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(sr[i + 1]), c, -msc));
-          rs4[h] += p0 + p1;
+          float x0, x1;
+          ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
+          const float p0 = ex2_approx(x0);
+          const float p1 = ex2_approx(x1);
+          fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
           pk[h] = pack_bf16x2(p0, p1);
         }
         uint8_t* pblk = prow + (ch >> 3) * TILE_BYTES;        // K-block of 64 keys
         *reinterpret_cast<uint4*>(pblk + (((ch & 7) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run = l_run * alpha + ((rs4[0] + rs4[1]) + (rs4[2] + rs4[3]));
+      l_run = l_run * alpha + (((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7])));
       m_run = m_new;
       tc_fence_before();
       fence_proxy_async_smem();          // generic-proxy stores of P -> visible to the tensor core (async proxy)
-      mbar_arrive(&p_full[g]);
+      mbar_arrive(&p_full[pb]);
       mbar_arrive(&s_empty[sb]);
       // ---- deferred accumulation of this group's previous tile: O <- (O + O_prev) * alpha ----
       if (it >= 1) {
@@ -267,7 +289,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           tmem_ld32(to + cc * 32, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = (o_acc[cc * 32 + i] + __uint_as_float(r[i])) * alpha;
+          for (int i = 0; i < 32; i += 2) {
+            fadd2(o_acc[cc * 32 + i], o_acc[cc * 32 + i + 1], __uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+            fmul2(o_acc[cc * 32 + i], o_acc[cc * 32 + i + 1], alpha);
+          }
         }
         tc_fence_before();
         mbar_arrive(&o_empty[g]);
@@ -290,6 +315,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // ---- merge the two streams: group 1 parks (m, l, O) in its own (now idle) P buffer, group 0 combines ----
     float* xch = reinterpret_cast<float*>(smem + OFF_P + 2 * TILE_BYTES);   // P[1]: 32 KiB = 128 rows x 64 fp32
     float* xml = reinterpret_cast<float*>(smem + OFF_XML);                  // 128 x {m, l}
+    asm volatile("bar.sync 2, 256;" ::: "memory");   // every P V product has completed: the P buffers are free
     if (g == 1) {
 #pragma unroll
       for (int i = 0; i < AT_D; ++i) xch[i * AT_BM + row] = o_acc[i];     // column-major: conflict-free
