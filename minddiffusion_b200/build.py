@@ -18,7 +18,7 @@ SOURCES = ["abi.cu", "gemm_tc.cu", "conv_direct.cu", "norm.cu", "attention.cu", 
            "glide_ops.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
-         "--use_fast_math" if os.environ.get("MDX_FAST_MATH") else "-DMDX_PRECISE", "-I" + os.path.join(HERE, "..", "include")]
+         "--use_fast_math" if os.environ.get("MDX_FAST_MATH") else "-DMDX_PRECISE", "-I" + os.path.join(HERE, "..", "include")] + os.environ.get("MDX_NVCC_EXTRA", "").split()
 
 
 def _digest():

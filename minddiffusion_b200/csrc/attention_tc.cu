@@ -10,9 +10,10 @@
 //   warp 2 : TMEM allocate / free (512 columns: 3 x 128 for S, 2 x 64 for O)
 //   warps 4-11: softmax, two warpgroups ping-ponging over key tiles (group g owns tiles g, g+2, ...).  Thread =
 //                           query row (TMEM lane), so row max / row sum need no shuffles.  Two passes over S in TMEM
-//                           (max, then exp2 + sum), P written as bf16 into a 128B-swizzled smem operand, running
-//                           output kept in fp32 registers: O <- (O + O_prev) * alpha, one tile late so that the P V
-//                           MMA overlaps the next softmax; the two groups' (max, sum, O) are merged at the end.
+//                           (max, then exp2 + sum), P written as bf16 into a 128B-swizzled smem operand.  The running
+//                           output O[g] stays in TMEM and accumulates over the group's tiles; it is rescaled in place
+//                           (tcgen05.ld / st) only when a row's max moves by more than 2^8; the two groups' (max, sum, O)
+//                           are merged at the end.
 // Keys beyond Nk are masked to -inf (K/V rows there are zero-filled by TMA); query rows beyond Nq are not stored.
 #include "common.cuh"
 #include <atomic>
@@ -26,7 +27,6 @@ constexpr int AT_BN = 128;   // keys per tile
 constexpr int AT_D = 64;
 constexpr int AT_KS = 3;     // K ring depth
 constexpr int AT_VS = 3;     // V ring depth
-constexpr int AT_PS = 3;     // P operand buffers (tile % 3): never waits for the P V product of the tile before
 constexpr int AT_SS = 3;     // S accumulators in TMEM: Q K^T runs two tiles ahead of the softmax
 constexpr int TILE_BYTES = 128 * 64 * 2;  // 16 KiB: one [128 x 64] bf16 operand block
 
@@ -41,8 +41,8 @@ struct AttnTcP {
 constexpr int OFF_Q = 0;
 constexpr int OFF_K = OFF_Q + TILE_BYTES;
 constexpr int OFF_V = OFF_K + AT_KS * TILE_BYTES;
-constexpr int OFF_P = OFF_V + AT_VS * TILE_BYTES;          // AT_PS buffers x 2 K-blocks
-constexpr int OFF_BAR = OFF_P + AT_PS * 2 * TILE_BYTES;
+constexpr int OFF_XCH = OFF_V + AT_VS * TILE_BYTES;        // 32 KiB: group 1 parks its O rows here for the final merge
+constexpr int OFF_BAR = OFF_XCH + 2 * TILE_BYTES;
 constexpr int OFF_XML = OFF_BAR + 512;
 constexpr int AT_SMEM = OFF_XML + 1024 + 1024;
 
@@ -70,6 +70,17 @@ __device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1) 
       : "+f"(d0), "+f"(d1)
       : "f"(a0), "f"(a1));
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,"
+      "%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void fmul2(float& d0, float& d1, float b) {
   asm("{\n\t.reg .b64 rb, rd;\n\tmov.b64 rb, {%2, %2};\n\tmov.b64 rd, {%0, %1};\n\tmul.rn.f32x2 rd, rd, rb;\n\t"
       "mov.b64 {%0, %1}, rd;\n\t}"
@@ -99,10 +110,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* v_full = k_empty + AT_KS;      // AT_VS
   uint64_t* v_empty = v_full + AT_VS;      // AT_VS
   uint64_t* s_full = v_empty + AT_VS;      // AT_SS
-  uint64_t* s_empty = s_full + AT_SS;      // AT_SS
-  uint64_t* p_full = s_empty + AT_SS;      // AT_PS
-  uint64_t* p_empty = p_full + AT_PS;      // AT_PS
-  uint64_t* o_full = p_empty + AT_PS;      // 2
+  uint64_t* p_full = s_full + AT_SS;       // AT_SS
+  uint64_t* o_full = p_full + AT_SS;       // 2
   uint64_t* o_empty = o_full + 2;          // 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
 
@@ -120,9 +129,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     mbar_init(q_full, 1);
     for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
     for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-    for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 128); }
-    for (int i = 0; i < AT_PS; ++i) { mbar_init(&p_full[i], 128); mbar_init(&p_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
+    for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
+    for (int i = 0; i < 2; ++i) mbar_init(&o_full[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -165,30 +173,30 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
       const uint32_t q_base = smem_u32(smem + OFF_Q);
       auto issue_pv = [&](int i) {
-        const int pb = i % AT_PS, vs = i % AT_VS, ob = i & 1;
-        mbar_wait(&p_full[pb], (i / AT_PS) & 1);
+        const int pb = i % AT_SS, vs = i % AT_VS, ob = i & 1;
+        mbar_wait(&p_full[pb], (i / AT_SS) & 1);
         mbar_wait(&v_full[vs], (i / AT_VS) & 1);
-        mbar_wait(&o_empty[ob], ((i >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t p_base = smem_u32(smem + OFF_P + pb * 2 * TILE_BYTES);
+        const uint32_t p_tmem = TM_S + pb * AT_BN;   // P_i (bf16 pairs, 64 columns) sits where S_i was
         const uint32_t v_base = smem_u32(smem + OFF_V + vs * TILE_BYTES);
 #pragma unroll
         for (int kk = 0; kk < AT_BN / 16; ++kk) {
-          const uint32_t a_addr = p_base + (kk >> 2) * TILE_BYTES + (kk & 3) * 32;  // K-block of 64 keys, 32 B per K16
           const uint32_t b_addr = v_base + kk * 16 * 128;                          // 16 key rows of 128 B
-          umma_bf16(TM_O + ob * AT_D, umma_desc_sw128(a_addr), umma_desc_sw128_mn(b_addr), idesc_o, kk != 0 ? 1u : 0u);
+          // A = P from TMEM (16 keys = 8 columns of bf16 pairs).  O[ob] accumulates over all of the group's tiles;
+          // the softmax rescales it in place when its row max moves
+          umma_bf16_ts(TM_O + ob * AT_D, p_tmem + kk * 8, umma_desc_sw128_mn(b_addr), idesc_o,
+                       (i >= 2 || kk != 0) ? 1u : 0u);
         }
         umma_commit(&o_full[ob]);
         umma_commit(&v_empty[vs]);
-        umma_commit(&p_empty[pb]);
       };
       mbar_wait(q_full, 0);
-      // issue order S0 S1 S2 PV0 S3 PV1 ...: S_j only needs the softmax of tile j-3 to have drained its buffer, so
-      // the scores of a group's next tile are complete before the group finishes its current one
+      // issue order S0 S1 S2 PV0 S3 PV1 ...: the scores of a group's next tile are complete before the group finishes
+      // its current one.  S_j reuses the TMEM buffer of S_{j-3} / P_{j-3}; P V_{j-3} was issued (after waiting for
+      // P_{j-3}) earlier in this thread's program order and tcgen05.mma executes in issue order, so no barrier is needed
       for (int j = 0; j < T; ++j) {
         const int ks = j % AT_KS, sb = j % AT_SS;
         mbar_wait(&k_full[ks], (j / AT_KS) & 1);
-        mbar_wait(&s_empty[sb], ((j / AT_SS) & 1) ^ 1);
         tc_fence_after();
         const uint32_t k_base = smem_u32(smem + OFF_K + ks * TILE_BYTES);
 #pragma unroll
@@ -213,12 +221,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int qw = warp & 3;
     const int row = qw * 32 + lane;                         // query row in the tile == TMEM lane
     const uint32_t lane_off = (uint32_t)(qw * 32) << 16;
-    float o_acc[AT_D];
-#pragma unroll
-    for (int i = 0; i < AT_D; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
     const float c = p.sl2;
-    const int swz = row & 7;
     const uint32_t to = TM_O + lane_off + g * AT_D;
 
     int it = 0;  // this group's iteration count (phase bit of its barriers)
@@ -248,57 +252,71 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mx3 = max3f(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
       }
       const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      const float m_new = fmaxf(m_run, mx);
-      const float alpha = ex2_approx((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
-      const float msc = m_new * c;
-      // ---- p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
-      const int pb = j % AT_PS;
-      uint8_t* prow = smem + OFF_P + pb * 2 * TILE_BYTES + row * 128;
-      mbar_wait(&p_empty[pb], ((j / AT_PS) & 1) ^ 1);
-      float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      const float nmsc = -msc;
+      // ---- lazy rescale: the running max only moves when the tile's max exceeds it by more than 2^8 in the exp2
+      //      domain (P then stays <= 256, exact in fp32 sums and fine in bf16); m = -inf on the first tile ----
+      float alpha = 1.f;
+      const bool moved = (mx - m_run) * c > 8.f;
+      if (moved) {
+        alpha = ex2_approx((m_run - mx) * c);              // first tile: exp2(-inf) = 0
+        l_run *= alpha;
+        m_run = mx;
+      }
+      if (it >= 1) {
+        // P V of this group's previous tile has landed in O[g] (the wait also keeps the phase bookkeeping in step);
+        // O[g] accumulates in TMEM across tiles and is touched only when some row of the warp moved its max
+        mbar_wait(&o_full[g], (it - 1) & 1);
+        if (__any_sync(0xffffffffu, moved)) {
+          tc_fence_after();
 #pragma unroll
-      for (int ch = 0; ch < AT_BN / 8; ++ch) {                // 16 chunks of 8 keys (16 B each)
-        uint32_t pk[4];
+          for (int cc = 0; cc < AT_D / 32; ++cc) {
+            uint32_t r[32];
+            tmem_ld32(to + cc * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float a0 = __uint_as_float(r[i]), a1 = __uint_as_float(r[i + 1]);
+              fmul2(a0, a1, alpha);
+              r[i] = __float_as_uint(a0);
+              r[i + 1] = __float_as_uint(a1);
+            }
+            tmem_st32(to + cc * 32, r);
+          }
+          tmem_st_wait();
+        }
+      }
+      // ---- p = exp2(s*c - m*c), row sum, bf16 P into the swizzled smem operand ----
+      float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const float nmsc = -m_run * c;
+      uint32_t pk[AT_BN / 2];
+#pragma unroll
+      for (int ch = 0; ch < AT_BN / 8; ++ch) {                // 16 chunks of 8 keys
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
           const int i = ch * 8 + h * 2;
           float x0, x1;
           ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
+#ifdef AT_DEBUG_NOEXP   /* profiling builds only: is the softmax MUFU-bound? */
+          const float p0 = x0, p1 = x1;
+#else
           const float p0 = ex2_approx(x0);
           const float p1 = ex2_approx(x1);
+#endif
           fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
-          pk[h] = pack_bf16x2(p0, p1);
+          pk[i >> 1] = pack_bf16x2(p0, p1);
         }
-        uint8_t* pblk = prow + (ch >> 3) * TILE_BYTES;        // K-block of 64 keys
-        *reinterpret_cast<uint4*>(pblk + (((ch & 7) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run = l_run * alpha + (((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7])));
-      m_run = m_new;
+      // P (bf16 pairs: key 2c in the low half of column c) over the first 64 columns of this tile's S buffer
+      tmem_st32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      tmem_st32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+      tmem_st_wait();
+      l_run += ((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7]));
       tc_fence_before();
-      fence_proxy_async_smem();          // generic-proxy stores of P -> visible to the tensor core (async proxy)
-      mbar_arrive(&p_full[pb]);
-      mbar_arrive(&s_empty[sb]);
-      // ---- deferred accumulation of this group's previous tile: O <- (O + O_prev) * alpha ----
-      if (it >= 1) {
-        mbar_wait(&o_full[g], (it - 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int cc = 0; cc < AT_D / 32; ++cc) {
-          uint32_t r[32];
-          tmem_ld32(to + cc * 32, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            fadd2(o_acc[cc * 32 + i], o_acc[cc * 32 + i + 1], __uint_as_float(r[i]), __uint_as_float(r[i + 1]));
-            fmul2(o_acc[cc * 32 + i], o_acc[cc * 32 + i + 1], alpha);
-          }
-        }
-        tc_fence_before();
-        mbar_arrive(&o_empty[g]);
-      }
+      mbar_arrive(&p_full[sb]);
     }
-    // this group's last P V
+    // ---- this group's output row: O[g] after its last P V ----
+    float o_acc[AT_D];
+#pragma unroll
+    for (int i = 0; i < AT_D; ++i) o_acc[i] = 0.f;
     if (it >= 1) {
       mbar_wait(&o_full[g], (it - 1) & 1);
       tc_fence_after();
@@ -308,14 +326,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         tmem_ld32(to + cc * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] += __uint_as_float(r[i]);
+        for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = __uint_as_float(r[i]);
       }
       tc_fence_before();
     }
     // ---- merge the two streams: group 1 parks (m, l, O) in its own (now idle) P buffer, group 0 combines ----
-    float* xch = reinterpret_cast<float*>(smem + OFF_P + 2 * TILE_BYTES);   // P[1]: 32 KiB = 128 rows x 64 fp32
+    float* xch = reinterpret_cast<float*>(smem + OFF_XCH);                  // 32 KiB = 128 rows x 64 fp32
     float* xml = reinterpret_cast<float*>(smem + OFF_XML);                  // 128 x {m, l}
-    asm volatile("bar.sync 2, 256;" ::: "memory");   // every P V product has completed: the P buffers are free
     if (g == 1) {
 #pragma unroll
       for (int i = 0; i < AT_D; ++i) xch[i * AT_BM + row] = o_acc[i];     // column-major: conflict-free
