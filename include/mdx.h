@@ -41,7 +41,7 @@ int64_t mdx_launch_count(void);
  * (openaimodel.py:205) / GEGLU product (attention.py:47-51) / emb add (openaimodel.py:199-200) as epilogues.
  *
  *  A: 1..3 K-segments. Segment s is a bf16 NHWC view [n_img, H, W, seg_c[s]] with pixel stride lda[s];
- *     seg_taps[s] is 9 (3x3, pad 1, stride 1) or 1 (1x1 / dense). seg_c[s] % 64 == 0.
+ *     seg_taps[s] is 9 (3x3, pad 1, stride 1) or 1 (1x1 / dense); 4 only with up_phase (below). seg_c[s] % 64 == 0.
  *     A dense matrix [M, K] is passed as n_img = 1, H = 1, W = M.
  *  B: bf16 [N, Ktot] row-major (K contiguous), Ktot = sum_s taps_s * seg_c[s], K order (segment, tap=(r,s), c).
  *  epilogue, in this order: + bias[n] (fp32, optional) ; + rowbias[img(p) * ld_rowbias + n] (fp32, optional)
@@ -72,6 +72,12 @@ typedef struct mdx_gemm_args {
   int32_t block_n;
   int32_t act; /* applied after bias/rowbias, before the residual: 0 none, 1 GELU (tanh form, nn.GELU() of
                   encoders/text_encoder.py:67-69), 2 QuickGELU x*sigmoid(1.702x) (wukong text_encoder.py:67-74) */
+  int32_t up_phase; /* 0 = off.  1..4: this launch computes phase (py, px) = ((up_phase-1) >> 1, (up_phase-1) & 1) of
+                  Upsample = nearest x2 followed by conv3x3 (openaimodel.py:53-63) WITHOUT materialising the
+                  upsampled image: output pixel (2y+py, 2x+px) only sees the 2x2 source window at offset
+                  (py-1, px-1), so segment 0 has seg_taps = 4 and B holds the phase's folded weights
+                  [N, (a, b, c)], a/b = window row/column (see fold_upsample_weights in unet.py).  out, residual
+                  and rowbias are addressed in the upsampled [n_img, 2H, 2W] image; H, W stay the source size. */
 } mdx_gemm_args;
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
 /* BLOCK_N the library would pick for a GEMM with N output columns (needed to pack GEGLU weights). */

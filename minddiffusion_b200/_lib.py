@@ -40,6 +40,7 @@ class GemmArgs(ctypes.Structure):
         ("geglu", c_int),
         ("block_n", c_int),
         ("act", c_int),
+        ("up_phase", c_int),
     ]
 
 

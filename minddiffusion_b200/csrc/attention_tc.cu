@@ -295,12 +295,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           const int i = ch * 8 + h * 2;
           float x0, x1;
           ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
-#ifdef AT_DEBUG_NOEXP   /* profiling builds only: is the softmax MUFU-bound? */
-          const float p0 = x0, p1 = x1;
-#else
           const float p0 = ex2_approx(x0);
           const float p1 = ex2_approx(x1);
-#endif
           fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
           pk[i >> 1] = pack_bf16x2(p0, p1);
         }

@@ -27,7 +27,10 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 struct TcParams {
   int nseg;
   int seg_kb[3];    // 64-wide channel blocks per tap
-  int seg_taps[3];  // 1 or 9
+  int seg_taps[3];  // 1, 9 (3x3) or 4 (2x2 window of one phase of a 2x-upsampled 3x3 conv)
+  int up_py, up_px; // phase of the upsampled output this launch produces (taps == 4)
+  int up;           // 1: output / residual rows are pixels (2y+py, 2x+px) of the [n, 2H, 2W] image
+  long long hw_out; // pixels per image in the output addressing
   int total_kb;
   int n_img, H, W;
   int tn, th, tw;
@@ -86,7 +89,7 @@ __device__ __forceinline__ float4 epi_load_add(const TcParams& p, long long pix,
     }
   }
   if (p.rowbias) {
-    const int img = (int)(pix / ((long long)p.H * p.W));
+    const int img = (int)(pix / p.hw_out);
     const float4 rb = __ldg(reinterpret_cast<const float4*>(p.rowbias + (long long)img * p.ld_rowbias + col));
     acc4.x += rb.x; acc4.y += rb.y; acc4.z += rb.z; acc4.w += rb.w;
   }
@@ -304,8 +307,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           const int taps = p.seg_taps[seg];
           const int nkb = p.seg_kb[seg];
           for (int tap = 0; tap < taps; ++tap) {
-            const int dy = taps == 9 ? tap / 3 - 1 : 0;
-            const int dx = taps == 9 ? tap % 3 - 1 : 0;
+            const int dy = taps == 9 ? tap / 3 - 1 : (taps == 4 ? p.up_py - 1 + (tap >> 1) : 0);
+            const int dx = taps == 9 ? tap % 3 - 1 : (taps == 4 ? p.up_px - 1 + (tap & 1) : 0);
             for (int cb = 0; cb < nkb; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
               mbar_arrive_expect_tx(&full[stage], stage_tx);
@@ -378,7 +381,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const int y = ((m_tile / p.tiles_x) % p.tiles_y) * p.th + yl;
       const int n = (m_tile / tiles_per_img_grid) * p.tn + nl;
       const bool valid = (x < p.W) && (y < p.H) && (n < p.n_img);
-      const long long pix_own = valid ? ((long long)n * p.H + y) * p.W + x : -1;
+      const long long pix_own = !valid ? -1
+                                : (p.up ? ((long long)n * 2 * p.H + 2 * y + p.up_py) * (2 * p.W) + 2 * x + p.up_px
+                                        : ((long long)n * p.H + y) * p.W + x);
 
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
@@ -648,7 +653,8 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     MDX_CHECK_ARG(a->a[s] != nullptr, "mdx_gemm_tc: A segment %d is NULL", s);
     MDX_CHECK_ARG(a->seg_c[s] > 0 && a->seg_c[s] % 64 == 0, "mdx_gemm_tc: seg_c[%d]=%d must be a multiple of 64", s,
                   a->seg_c[s]);
-    MDX_CHECK_ARG(a->seg_taps[s] == 1 || a->seg_taps[s] == 9, "mdx_gemm_tc: seg_taps[%d] must be 1 or 9", s);
+    MDX_CHECK_ARG(a->seg_taps[s] == 1 || a->seg_taps[s] == 9 || (a->seg_taps[s] == 4 && a->up_phase),
+                  "mdx_gemm_tc: seg_taps[%d] must be 1 or 9 (or 4 with up_phase)", s);
     MDX_CHECK_ARG((reinterpret_cast<uintptr_t>(a->a[s]) & 15) == 0 && a->lda[s] % 8 == 0 && a->lda[s] >= a->seg_c[s],
                   "mdx_gemm_tc: A segment %d must be 16-byte aligned with lda %% 8 == 0", s);
     p.seg_kb[s] = a->seg_c[s] / 64;
@@ -676,6 +682,15 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   p.residual = a->residual; p.ldr = a->ldr; p.res_f32 = a->residual_dtype == MDX_F32;
   p.geglu = a->geglu;
   p.act = a->act;
+  p.hw_out = (long long)a->H * a->W;
+  if (a->up_phase) {
+    MDX_CHECK_ARG(a->up_phase >= 1 && a->up_phase <= 4 && a->nseg == 1 && a->seg_taps[0] == 4 && !a->geglu,
+                  "mdx_gemm_tc: up_phase needs 1..4, one segment with 4 taps, no geglu");
+    p.up = 1;
+    p.up_py = (a->up_phase - 1) >> 1;
+    p.up_px = (a->up_phase - 1) & 1;
+    p.hw_out *= 4;
+  }
 
   CUtensorMap maps[3];
   for (int s = 0; s < 3; ++s) {

@@ -63,7 +63,7 @@ ACT = {None: 0, "gelu": 1, "quick_gelu": 2}
 
 
 def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
-            block_n=0, act=None):
+            block_n=0, act=None, up_phase=0):
     """Tensor-core implicit GEMM (mdx_gemm_tc).
 
     segs: list of (a, taps); a is bf16 ``[n, H, W, C]`` (conv view) or ``[M, C]`` (dense), taps 9 or 1.
@@ -94,7 +94,9 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
     if weight.shape[1] != ktot:
         raise ValueError("weight K=%d does not match segments K=%d" % (weight.shape[1], ktot))
     n_out = N // 2 if geglu else N
-    M = n_img * H * W
+    M = n_img * H * W * (4 if up_phase else 1)   # up_phase: out / residual are the 2x-upsampled image
+    if up_phase and out is None:
+        raise ValueError("up_phase launches write one phase of a caller-provided [n, 2H, 2W, N] buffer")
     if out is None:
         out = torch.empty((M, n_out), dtype=out_dtype, device=a0.device)
     orow, oc, ldc = _rows_ld(out)
@@ -122,12 +124,13 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
     args.geglu = 1 if geglu else 0
     args.block_n = block_n
     args.act = ACT[act]
+    args.up_phase = up_phase
     if GEMM_TC_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         check(lib.mdx_gemm_tc(ctypes.byref(args), _stream()), "mdx_gemm_tc")
         e1.record()
-        GEMM_TC_PROFILE.append((2.0 * M * N * ktot, e0, e1, (M, N, ktot, [t for _, t in segs], str(out.dtype)[6:],
+        GEMM_TC_PROFILE.append((2.0 * (M // (4 if up_phase else 1)) * N * ktot, e0, e1, (M, N, ktot, [t for _, t in segs], str(out.dtype)[6:],
                                                                None if residual is None else str(residual.dtype)[6:],
                                                                bool(geglu), rowbias is not None)))
         return out

@@ -199,7 +199,11 @@ class UNetModel:
             elif kind == "down":
                 L[pre + "op"] = (self._w(self._conv_k(g(pre + "op.conv.weight"))), g(pre + "op.conv.bias"))
             elif kind == "up":
-                L[pre + "up"] = (self._w(self._conv_k(g(pre + "conv.conv.weight"))), g(pre + "conv.conv.bias"))
+                w = g(pre + "conv.conv.weight")
+                if self.bf16:  # four 2x2 phase kernels instead of a 3x3 over the upsampled image
+                    L[pre + "up"] = ([self._w(wp) for wp in fold_upsample_weights(w)], g(pre + "conv.conv.bias"))
+                else:
+                    L[pre + "up"] = (self._w(self._conv_k(w)), g(pre + "conv.conv.bias"))
 
         for bi, block in enumerate(self.inp):
             for li, layer in enumerate(block):
@@ -325,7 +329,7 @@ class UNetModel:
     def _up(self, pre, x):
         w, b = self.L[pre + "up"]
         if self.bf16:
-            return self._conv3(ops.upsample_nearest2x(x, out_dtype=self.dtype), w, b, trunk=True)
+            return upsample_conv3x3(ops.cast(x, self.dtype), w, b, torch.float32)
         return ops.conv_direct(x, w, 3, 3, 1, 1, upsample=True, bias=b)
 
     # ------------------------------------------------------------------------------------------------
@@ -453,6 +457,37 @@ class UNetModel:
             self.set_context(context)
         out = self.forward_nhwc(x, timesteps)
         return ops.nhwc_to_nchw(out.contiguous(), self.out_channels)
+
+
+def fold_upsample_weights(w):
+    """Upsample = nearest x2 then conv3x3 (openaimodel.py:53-63).  Output pixel (2y+py, 2x+px) reads upsampled rows
+    2y+py+r, r in {-1, 0, 1}, i.e. source rows floor((2y+py+r)/2): for py = 0 {y-1 | y, y}, for py = 1 {y, y | y+1}.
+    So each output phase is a 2x2 convolution of the SOURCE image whose taps are sums of the 3x3 taps that land on
+    the same source pixel: 4/9 of the multiply-adds and no upsampled operand.  Returns the four phase matrices
+    [Cout, (a, b, c)] in phase order (py, px) = (0,0), (0,1), (1,0), (1,1); window offset is (py-1, px-1)."""
+    groups = {0: ((0,), (1, 2)), 1: ((0, 1), (2,))}   # phase -> kernel rows (or columns) folded into window tap 0 / 1
+    out = []
+    for py in (0, 1):
+        for px in (0, 1):
+            taps = []
+            for a in (0, 1):
+                for b_ in (0, 1):
+                    acc = 0
+                    for r in groups[py][a]:
+                        for c in groups[px][b_]:
+                            acc = acc + w[:, :, r, c]
+                    taps.append(acc)                       # [Cout, Cin]
+            out.append(torch.stack(taps, dim=1).reshape(w.shape[0], -1).contiguous())
+    return out
+
+
+def upsample_conv3x3(x, phase_weights, bias, out_dtype):
+    """x: bf16 NHWC [n, H, W, C] -> conv3x3(nearest_x2(x)) as [n, 2H, 2W, Cout], four mdx_gemm_tc launches."""
+    n, H, W, _ = x.shape
+    out = torch.empty((n, 2 * H, 2 * W, phase_weights[0].shape[0]), dtype=out_dtype, device=x.device)
+    for ph, wp in enumerate(phase_weights):
+        ops.gemm_tc([(x, 4)], wp, out=out.view(n * 4 * H * W, -1), bias=bias, up_phase=ph + 1)
+    return out
 
 
 def pack_geglu(w, b):

@@ -111,3 +111,33 @@ def test_gemm_tc_resident_weights(M, K, N, geglu):
     assert torch.equal(out, out_stream)
     err = float((out.float().cpu() - ref).abs().max() / ref.abs().max())
     assert err < tol, err
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,H,W,Cin,Cout", [(2, 8, 8, 64, 64), (1, 16, 16, 128, 320), (3, 5, 7, 64, 128), (2, 32, 32, 64, 160)])
+def test_upsample_conv_phase_folding(n, H, W, Cin, Cout):
+    """Upsample (nearest x2) + conv3x3 as four 2x2 phase GEMMs over the source image (gemm_tc up_phase) against
+    torch's interpolate + conv2d on the same bf16-rounded operands; also with a residual in the upsampled layout."""
+    from minddiffusion_b200 import ops
+    from minddiffusion_b200.unet import fold_upsample_weights, upsample_conv3x3
+    g = torch.Generator().manual_seed(n * H + Cin + Cout)
+    x = torch.randn(n, H, W, Cin, generator=g).bfloat16()
+    w = (torch.randn(Cout, Cin, 3, 3, generator=g) / (9 * Cin) ** 0.5)
+    b = torch.randn(Cout, generator=g)
+    up = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest")
+    ref = F.conv2d(up, w, b, padding=1).permute(0, 2, 3, 1)
+    wp = [p.cuda().bfloat16() for p in fold_upsample_weights(w)]
+    out = upsample_conv3x3(x.cuda(), wp, b.cuda(), torch.float32)
+    assert tuple(out.shape) == (n, 2 * H, 2 * W, Cout)
+    err = float((out.cpu() - ref).abs().max() / ref.abs().max())
+    assert err < 1e-2, err          # folded taps are rounded to bf16 once more than the 3x3 taps
+    # exact fold: with weights that are exactly representable the phase GEMMs reproduce the 3x3 result to fp32 rounding
+    wq = torch.randint(-2, 3, (Cout, Cin, 3, 3), generator=g).float() / 8
+    ref = F.conv2d(up, wq, b, padding=1).permute(0, 2, 3, 1)
+    res = torch.randn(n, 2 * H, 2 * W, Cout, generator=g)
+    outq = torch.empty(n, 2 * H, 2 * W, Cout, device="cuda")
+    for ph, p in enumerate(fold_upsample_weights(wq)):
+        ops.gemm_tc([(x.cuda(), 4)], p.cuda().bfloat16(), out=outq.view(-1, Cout), bias=b.cuda(),
+                    residual=res.cuda().view(-1, Cout), up_phase=ph + 1)
+    err = float((outq.cpu() - (ref + res)).abs().max() / ref.abs().max())
+    assert err < 1e-5, err
