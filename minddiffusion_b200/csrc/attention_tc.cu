@@ -368,6 +368,155 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Single-tile variant: Nk <= 128 (the cross-attention over 77 text tokens, attention.py:118-152).  There is no
+// key loop to pipeline, so the CTA is small (4 role warps + ONE softmax warpgroup, 48 KiB smem, 128 TMEM columns:
+// S, then P over its first half and O over its second) and two CTAs share an SM to overlap each other's
+// TMA -> MMA -> softmax -> MMA -> store latency chain.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int AT1_SMEM = 3 * TILE_BYTES + 256 + 1024;
+
+__global__ void __launch_bounds__(256, 2)
+attn_tc_single_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const AttnTcP p) {
+  extern __shared__ uint8_t at_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 3 * TILE_BYTES);
+  uint64_t* qk_full = bars;       // Q and K landed
+  uint64_t* v_full = bars + 1;
+  uint64_t* s_full = bars + 2;
+  uint64_t* p_full = bars + 3;
+  uint64_t* o_full = bars + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * AT_BM;
+  const int head = blockIdx.y, b = blockIdx.z;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(qk_full, 1);
+    mbar_init(v_full, 1);
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 128);
+    mbar_init(o_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int ksteps = (p.Nk + 15) / 16;          // P V only over the 16-key blocks that hold real keys
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (warp == 0) {
+      if (elect_one()) {
+        mbar_arrive_expect_tx(qk_full, 2 * TILE_BYTES);
+        tma_load_3d(smem, &tmQ, qk_full, head * AT_D, q0, b);
+        tma_load_3d(smem + TILE_BYTES, &tmK, qk_full, head * AT_D, 0, b);
+        mbar_arrive_expect_tx(v_full, TILE_BYTES);
+        tma_load_3d(smem + 2 * TILE_BYTES, &tmV, v_full, head * AT_D, 0, b);
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+        constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+        const uint32_t q_base = smem_u32(smem), k_base = smem_u32(smem + TILE_BYTES);
+        const uint32_t v_base = smem_u32(smem + 2 * TILE_BYTES);
+        mbar_wait(qk_full, 0);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < AT_D / 16; ++k)
+          umma_bf16(tmem_base, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s, k != 0 ? 1u : 0u);
+        umma_commit(s_full);
+        mbar_wait(p_full, 0);
+        mbar_wait(v_full, 0);
+        tc_fence_after();
+        for (int kk = 0; kk < ksteps; ++kk)
+          umma_bf16_ts(tmem_base + 64, tmem_base + kk * 8, umma_desc_sw128_mn(v_base + kk * 16 * 128), idesc_o,
+                       kk != 0 ? 1u : 0u);
+        umma_commit(o_full);
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    const int qw = warp & 3;
+    const int row = qw * 32 + lane;
+    const uint32_t ts = tmem_base + ((uint32_t)(qw * 32) << 16);
+    const float c = p.sl2;
+    mbar_wait(s_full, 0);
+    tc_fence_after();
+    uint32_t sr[AT_BN];
+#pragma unroll
+    for (int cc = 0; cc < AT_BN / 32; ++cc)
+      if (cc * 32 < p.Nk) tmem_ld32(ts + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < AT_BN; ++i)
+      if (i >= p.Nk) sr[i] = 0xff800000u;            // keys beyond Nk (and the column groups not loaded) count as -inf
+    float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < AT_BN; i += 8) {
+      mx0 = max3f(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+      mx1 = max3f(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+      mx2 = max3f(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
+      mx3 = max3f(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
+    }
+    const float nmsc = -fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * c;
+    float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    uint32_t pk[AT_BN / 2];
+#pragma unroll
+    for (int i = 0; i < AT_BN; i += 2) {
+      float x0, x1;
+      ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
+      const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+      fadd2(rs8[i & 6], rs8[(i & 6) + 1], p0, p1);
+      pk[i >> 1] = pack_bf16x2(p0, p1);
+    }
+    const float l = ((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7]));
+    tmem_st32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+    tmem_st32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+    tmem_st_wait();
+    tc_fence_before();
+    mbar_arrive(p_full);
+    const float inv = 1.f / l;
+    mbar_wait(o_full, 0);
+    tc_fence_after();
+    uint32_t r[AT_D];
+    tmem_ld32(ts + 64, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+    tmem_ld32(ts + 96, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+    tmem_ld_wait();
+    tc_fence_before();
+    if (q0 + row < p.Nq) {
+      bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * AT_D;
+#pragma unroll
+      for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+        uint4 u;
+        u.x = pack_bf16x2(__uint_as_float(r[v8 * 8]) * inv, __uint_as_float(r[v8 * 8 + 1]) * inv);
+        u.y = pack_bf16x2(__uint_as_float(r[v8 * 8 + 2]) * inv, __uint_as_float(r[v8 * 8 + 3]) * inv);
+        u.z = pack_bf16x2(__uint_as_float(r[v8 * 8 + 4]) * inv, __uint_as_float(r[v8 * 8 + 5]) * inv);
+        u.w = pack_bf16x2(__uint_as_float(r[v8 * 8 + 6]) * inv, __uint_as_float(r[v8 * 8 + 7]) * inv);
+        *reinterpret_cast<uint4*>(orow + v8 * 8) = u;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -421,13 +570,17 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
   static bool attr_set = false;
   if (!attr_set) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT1_SMEM));
     attr_set = true;
   }
   AttnTcP p;
   p.Nq = Nq; p.Nk = Nk; p.sl2 = scale * 1.4426950408889634f;
   p.o = reinterpret_cast<bf16*>(o); p.ldo = ldo;
   dim3 grid((Nq + AT_BM - 1) / AT_BM, heads, batch);
-  attn_tc_kernel<<<grid, 384, AT_SMEM, st>>>(mq, mk, mv, p);
+  if (Nk <= AT_BN && !getenv("MDX_ATTN_NO_SINGLE"))
+    attn_tc_single_kernel<<<grid, 256, AT1_SMEM, st>>>(mq, mk, mv, p);
+  else
+    attn_tc_kernel<<<grid, 384, AT_SMEM, st>>>(mq, mk, mv, p);
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;

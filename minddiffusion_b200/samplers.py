@@ -86,10 +86,10 @@ class _GuidedUNet:
     def __call__(self, x, t_value):
         if self.split is not None:
             t = torch.full((x.shape[0],), float(t_value), dtype=torch.float32, device=x.device)
-            return self.split.exchange(self.unet.forward_nhwc(x, t, repeat=1))  # [uncond half | cond half]
+            return self.split.exchange(self.unet.forward_nhwc(x, t, repeat=1, uniform_t=True))  # [uncond | cond]
         n = x.shape[0] * (2 if self.cfg else 1)
         t = torch.full((n,), float(t_value), dtype=torch.float32, device=x.device)
-        return self.unet.forward_nhwc(x, t, repeat=2 if self.cfg else 1)
+        return self.unet.forward_nhwc(x, t, repeat=2 if self.cfg else 1, uniform_t=True)
 
 
 class PLMSSampler(object):

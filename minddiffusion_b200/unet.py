@@ -367,15 +367,19 @@ class UNetModel:
             for li, layer in enumerate(block):
                 visit("output_blocks.%d.%d." % (bi, li), layer)
 
-    def _forward_impl(self, x_nchw, t, repeat, taps=None):
+    def _forward_impl(self, x_nchw, t, repeat, taps=None, uniform_t=False):
         L = self.L
         n = x_nchw.shape[0] * repeat
         self._gn_scratch = torch.empty(n * 64, dtype=torch.float64, device=self.device)
-        # timestep embedding + time_embed MLP + every ResBlock's emb_layers, all fp32 (tiny)
-        t_emb = ops.timestep_embedding(t, self.model_channels)
+        # timestep embedding + time_embed MLP + every ResBlock's emb_layers, all fp32 (tiny).  The sampler loops
+        # evaluate the whole batch at ONE timestep (plms.py:118, ddim ts = full((b,), step)): one row is computed and
+        # every image reads it (row stride 0 of the per-image bias).
+        t_emb = ops.timestep_embedding(t[:1] if uniform_t else t, self.model_channels)
         emb = ops.conv_direct(t_emb, L["te0"][0], bias=L["te0"][1])
         emb = ops.conv_direct(emb, L["te2"][0], bias=L["te2"][1], pre_silu=True)
         emb_all = ops.conv_direct(emb, L["emb_all"][0], bias=L["emb_all"][1], pre_silu=True)  # [n, sum Cout]
+        if uniform_t:
+            emb_all = emb_all.expand(n, -1)
         h = ops.nchw_to_nhwc(x_nchw, self.dtype, repeat=repeat, cpad=self.cin_pad)
         hs = []
 
@@ -415,7 +419,7 @@ class UNetModel:
             return ops.gemm_tc([(h, 9)], w, bias=b, out_dtype=torch.float32).view(nn_, H, W, -1)
         return ops.conv_direct(h, w, 3, 3, 1, 1, bias=b)
 
-    def forward_nhwc(self, x_nchw, timesteps, repeat=1, taps=None):
+    def forward_nhwc(self, x_nchw, timesteps, repeat=1, taps=None, uniform_t=False):
         """x_nchw: fp32 [B, C, H, W]; timesteps: [B*repeat] (any numeric dtype); the batch is read `repeat` times
         (repeat=2 is the CFG concat of plms.py:192-194 without the copy).  Returns fp32 NHWC [B*repeat, H, W, ld]
         with ld >= out_channels (bf16 mode pads conv_out to 16 columns)."""
@@ -429,17 +433,17 @@ class UNetModel:
         if t.numel() != n:
             raise ValueError("timesteps must have %d entries" % n)
         if not self.use_cuda_graph or taps is not None:
-            return self._forward_impl(x_nchw, t, repeat, taps)
-        key = (tuple(x_nchw.shape), repeat)
+            return self._forward_impl(x_nchw, t, repeat, taps, uniform_t)
+        key = (tuple(x_nchw.shape), repeat, uniform_t)
         ent = self._graphs.get(key)
         if ent is None:
             sx, st_ = x_nchw.clone(), t.clone()
-            self._forward_impl(sx, st_, repeat)  # warm-up: sets kernel attributes, fills the allocator
+            self._forward_impl(sx, st_, repeat, None, uniform_t)  # warm-up: sets kernel attributes, fills the allocator
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
-                sout = self._forward_impl(sx, st_, repeat)
+                sout = self._forward_impl(sx, st_, repeat, None, uniform_t)
             ent = (graph, sx, st_, sout, _lib.launch_count() - n0)
             self._graphs[key] = ent
         graph, sx, st_, sout, nk = ent

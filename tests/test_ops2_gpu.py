@@ -141,3 +141,29 @@ def test_upsample_conv_phase_folding(n, H, W, Cin, Cout):
                     residual=res.cuda().view(-1, Cout), up_phase=ph + 1)
     err = float((outq.cpu() - (ref + res)).abs().max() / ref.abs().max())
     assert err < 1e-5, err
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,heads,Nq,Nk", [(2, 5, 300, 77), (1, 3, 128, 128), (2, 2, 64, 1), (1, 4, 513, 16), (3, 2, 200, 100)])
+def test_single_tile_attention_kernel(B, heads, Nq, Nk):
+    """Nk <= 128 runs the small two-CTA-per-SM kernel (attention_tc.cu, attn_tc_single_kernel); it must agree with
+    the general kernel (MDX_ATTN_NO_SINGLE=1) to bf16 rounding and with an fp32 torch softmax."""
+    import os
+    from minddiffusion_b200 import ops
+    d, C = 64, heads * 64
+    g = torch.Generator().manual_seed(B * Nq + Nk)
+    q = torch.randn(B, Nq, C, generator=g).bfloat16()
+    kv = torch.randn(B, Nk, 2 * C, generator=g).bfloat16()
+    sp = lambda t, n: t.float().reshape(B, n, heads, d).permute(0, 2, 1, 3)
+    s = torch.matmul(sp(q, Nq), sp(kv[..., :C], Nk).transpose(-1, -2)) * d ** -0.5
+    ref = torch.matmul(torch.softmax(s, -1), sp(kv[..., C:], Nk)).permute(0, 2, 1, 3).reshape(B, Nq, C)
+    kvd = kv.cuda()
+    out = ops.attention(q.cuda(), kvd[..., :C], kvd[..., C:], heads, d ** -0.5)
+    os.environ["MDX_ATTN_NO_SINGLE"] = "1"
+    try:
+        out_general = ops.attention(q.cuda(), kvd[..., :C], kvd[..., C:], heads, d ** -0.5)
+    finally:
+        del os.environ["MDX_ATTN_NO_SINGLE"]
+    scale = float(ref.abs().max())
+    assert float((out.float().cpu() - ref).abs().max()) / scale < 2e-2
+    assert float((out.float() - out_general.float()).abs().max()) / scale < 1e-2
