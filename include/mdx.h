@@ -78,8 +78,17 @@ typedef struct mdx_gemm_args {
                   (py-1, px-1), so segment 0 has seg_taps = 4 and B holds the phase's folded weights
                   [N, (a, b, c)], a/b = window row/column (see fold_upsample_weights in unet.py).  out, residual
                   and rowbias are addressed in the upsampled [n_img, 2H, 2W] image; H, W stay the source size. */
+  float* chan_stats; /* optional [n_img, slots, 2, N] fp32 (16-byte aligned, need not be initialised), slots =
+                  mdx_gemm_tc_stat_slots(n_img, H, W, up_phase != 0): for every 32 output rows (one slot) the epilogue
+                  stores the per-channel sum (plane 0) and sum of squares (plane 1) of the values it wrote — the
+                  GroupNorm statistics of the tensor's consumer (mdx_groupnorm_pre), so that no separate pass
+                  re-reads the activation.  No atomics: each slot is written once and the consumer adds the slots in
+                  a fixed order.  The four up_phase launches of one tensor fill disjoint slots of one array.
+                  Needs images of >= 128 pixels (mdx_gemm_tc_stat_slots returns 0 otherwise). */
 } mdx_gemm_args;
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
+/* Statistics slots per image for mdx_gemm_args.chan_stats (0: images too small, use the two-pass GroupNorm). */
+int mdx_gemm_tc_stat_slots(int32_t n_img, int32_t H, int32_t W, int32_t up);
 /* BLOCK_N the library would pick for a GEMM with N output columns (needed to pack GEGLU weights). */
 int mdx_gemm_tc_pick_block_n(int32_t N, int32_t geglu);
 
@@ -130,6 +139,16 @@ int mdx_groupnorm(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64
                   void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
                   double* stats_scratch, void* stream);
 
+/* mdx_groupnorm_pre: mdx_groupnorm (and, with scale_shift != NULL, mdx_groupnorm_film) without the statistics pass.
+ *  chan1 / chan2: [n, slots1, 2, C1] / [n, slots2, 2, C2] fp32 partial sums written by the producers of x1 / x2
+ *  (mdx_gemm_args.chan_stats).  A small kernel (one warp per image and group, fixed order) folds them into the
+ *  per-group sums — any grouping of concat(x1, x2), so the skip concat of openaimodel.py:566-571 works even where
+ *  a group straddles the two tensors — then the apply pass runs. */
+int mdx_groupnorm_pre(const void* x1, int64_t ld1, int32_t C1, const float* chan1, int32_t slots1, const void* x2,
+                      int64_t ld2, int32_t C2, const float* chan2, int32_t slots2, int32_t n, int32_t HW,
+                      int32_t groups, float eps, const float* gamma, const float* beta, const float* scale_shift,
+                      int64_t ld_ss, int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw,
+                      int32_t in_dtype, int32_t out_dtype, double* stats_scratch, void* stream);
 /* GroupNorm without caller scratch.  (No counterpart in the reference: MindSpore hands its kernels a workspace;
  * this exists for callers of THIS library that cannot provide one.)
  * Same operands and dtype pairs as mdx_groupnorm, minus stats_scratch: the per-group sums live in a fixed

@@ -41,6 +41,7 @@ class GemmArgs(ctypes.Structure):
         ("block_n", c_int),
         ("act", c_int),
         ("up_phase", c_int),
+        ("chan_stats", c_p),
     ]
 
 
@@ -89,6 +90,9 @@ SIGNATURES = {
                                       c_int, c_int, c_int, c_int, c_p]),
     "mdx_sampler_dpmpp2m_step": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_int, c_p, c_p, c_p, c_p, c_p, c_int, c_int,
                                          c_int, c_int, c_p]),
+    "mdx_groupnorm_pre": (c_int, [c_p, c_i64, c_int, c_p, c_int, c_p, c_i64, c_int, c_p, c_int, c_int, c_int, c_int, c_f,
+                                  c_p, c_p, c_p, c_i64, c_int, c_p, c_i64, c_p, c_i64, c_int, c_int, c_p, c_p]),
+    "mdx_gemm_tc_stat_slots": (c_int, [c_int, c_int, c_int, c_int]),
     "mdx_groupnorm_film": (c_int, [c_p, c_i64, c_int, c_int, c_int, c_int, c_f, c_p, c_p, c_p, c_i64, c_int, c_p, c_i64,
                                    c_int, c_int, c_p, c_p]),
     "mdx_avgpool2x2": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p, c_int, c_int, c_p]),

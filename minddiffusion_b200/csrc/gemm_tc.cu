@@ -37,6 +37,9 @@ struct TcParams {
   int tiles_x, tiles_y;
   int N, n_tiles_n, num_tiles;
   int m_tiles;
+  float* chan_stats;   // optional [n_img][slots][2][N]: per-(image, 32-row slot, channel) sum / sum of squares of the
+                       // stored output; slot = (phase *) tile-in-image * 4 + lane quadrant, every slot written once
+  int stat_slots;      // slots per image
   int debug;        // MDX_GEMM_DEBUG bit mask (profiling only): 1 = no global stores, 2 = epilogue does nothing
   int b_resident;   // K fits the B ring: each CTA keeps ONE n-tile's weight slice in smem and streams only A tiles
   void* out;
@@ -98,7 +101,7 @@ __device__ __forceinline__ float4 epi_load_add(const TcParams& p, long long pix,
 
 template <int BN, bool OUT_F32, bool HAS_ADD>
 __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint32_t stg, int lane, int cpar,
-                                         int cstep, int n_tile, long long pix_own) {
+                                         int cstep, int n_tile, long long pix_own, long long stat_slot) {
   const int n_out = p.N;
   const int ocol_tile = n_tile * BN;
   const int sr8 = lane >> 2, q4 = lane & 3;
@@ -187,6 +190,7 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
 #pragma unroll
       for (int j = 0; j < 4; ++j) sts128(stg + lane * 80 + 16 * j, r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
       __syncwarp();
+      float cs[4] = {0.f, 0.f, 0.f, 0.f}, cq[4] = {0.f, 0.f, 0.f, 0.f};   // column sums over this lane's rows
 #pragma unroll
       for (int pass = 0; pass < 4; ++pass) {
         const uint4 u = lds128(stg + (pass * 8 + sr8) * 80 + q4 * 16);
@@ -205,6 +209,33 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
           w.x = pack_bf16x2(o.x, o.y);
           w.y = pack_bf16x2(o.z, o.w);
           *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(p.out) + pix * p.ldc + col) = w;
+          if (p.chan_stats) {   // the statistics are those of the values a reader of `out` sees
+            const float2 lo = unpack_bf16x2(w.x), hi = unpack_bf16x2(w.y);
+            o = make_float4(lo.x, lo.y, hi.x, hi.y);
+          }
+        }
+        if (p.chan_stats) {
+          cs[0] += o.x; cs[1] += o.y; cs[2] += o.z; cs[3] += o.w;
+          cq[0] = fmaf(o.x, o.x, cq[0]); cq[1] = fmaf(o.y, o.y, cq[1]);
+          cq[2] = fmaf(o.z, o.z, cq[2]); cq[3] = fmaf(o.w, o.w, cq[3]);
+        }
+      }
+      if (p.chan_stats && stat_slot >= 0) {
+        // GroupNorm statistics for the consumer of this tensor (mdx_groupnorm_pre): reduce the 8 lanes that hold
+        // the same 4 columns (lane = 4*row_lane + q4); lanes 0..3 store the warp's partial sums into its own slot —
+        // no atomics, every slot is written exactly once, the consumer adds the slots in a fixed order
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+          for (int m = 4; m < 32; m <<= 1) {
+            cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], m);
+            cq[k] += __shfl_xor_sync(0xffffffffu, cq[k], m);
+          }
+        }
+        if (lane < 4 && col_ok) {
+          float* dst = p.chan_stats + (long long)stat_slot * 2 * p.N + col;
+          *reinterpret_cast<float4*>(dst) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+          *reinterpret_cast<float4*>(dst + p.N) = make_float4(cq[0], cq[1], cq[2], cq[3]);
         }
       }
       if constexpr (HAS_ADD) {
@@ -371,7 +402,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const int yl = (row / p.tw) % p.th;
     const int nl = row / (p.tw * p.th);
     const uint32_t stg = smem_u32(smem + Cfg::STAGING_OFF) + ew * Cfg::STG_BYTES;
-    const bool has_add = p.residual != nullptr || p.rowbias != nullptr;
+    // chan_stats rides on the general path (its coalesced phase sees fp32 values of whole rows)
+    const bool has_add = p.residual != nullptr || p.rowbias != nullptr || p.chan_stats != nullptr;
     uint32_t iter = 0;
     int m_tile, n_tile;
     for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
@@ -388,6 +420,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + as * BN;
+      // statistics slot of this warp's 32 rows: (image, [phase,] tile inside the image, lane quadrant); tn == 1
+      long long stat_slot = -1;
+      if (p.chan_stats) {
+        const int img = m_tile / tiles_per_img_grid;
+        const int in_img = (p.up ? (p.up_py * 2 + p.up_px) * tiles_per_img_grid : 0) + m_tile % tiles_per_img_grid;
+        stat_slot = (long long)img * p.stat_slots + in_img * 4 + qw;
+      }
 
       if (p.debug & 2) {
         // profiling only: drop the tile
@@ -459,11 +498,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           }
         }
       } else if (p.out_f32) {
-        if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
-        else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
+        if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
+        else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
       } else {
-        if (has_add) epi_tile<BN, false, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
-        else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own);
+        if (has_add) epi_tile<BN, false, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
+        else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
       }
       tc_fence_before();
       mbar_arrive(&tempty[as]);
@@ -621,6 +660,14 @@ extern "C" int mdx_gemm_tc_pick_block_n(int32_t N, int32_t geglu) {
   return best;
 }
 
+extern "C" int mdx_gemm_tc_stat_slots(int32_t n_img, int32_t H, int32_t W, int32_t up) {
+  if (n_img <= 0 || H <= 0 || W <= 0) return 0;
+  int tw, th, tn;
+  pick_tile(W, H, n_img, &tw, &th, &tn);
+  if (tn != 1) return 0;
+  return ((W + tw - 1) / tw) * ((H + th - 1) / th) * 4 * (up ? 4 : 1);
+}
+
 extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   MDX_CHECK_ARG(a != nullptr, "mdx_gemm_tc: args is NULL");
   MDX_CHECK_ARG(a->nseg >= 1 && a->nseg <= 3, "mdx_gemm_tc: nseg must be 1..3 (got %d)", a->nseg);
@@ -677,11 +724,20 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   MDX_CHECK_ARG(nt < (1ll << 31), "mdx_gemm_tc: too many tiles");
   p.num_tiles = (int)nt;
   p.m_tiles = p.tiles_x * p.tiles_y * tiles_n;
+  if (a->chan_stats) {
+    MDX_CHECK_ARG(p.tn == 1, "mdx_gemm_tc: chan_stats needs images of at least 128 pixels (got %d x %d)", a->H, a->W);
+    p.stat_slots = p.tiles_x * p.tiles_y * 4 * (a->up_phase ? 4 : 1);
+  }
   p.out = a->out; p.ldc = a->ldc; p.out_f32 = a->out_dtype == MDX_F32;
   p.bias = a->bias; p.rowbias = a->rowbias; p.ld_rowbias = a->ld_rowbias;
   p.residual = a->residual; p.ldr = a->ldr; p.res_f32 = a->residual_dtype == MDX_F32;
   p.geglu = a->geglu;
   p.act = a->act;
+  p.chan_stats = a->chan_stats;
+  if (a->chan_stats)
+    MDX_CHECK_ARG(!a->geglu && (reinterpret_cast<uintptr_t>(a->chan_stats) & 15) == 0,
+                  "mdx_gemm_tc: chan_stats excludes geglu and must be 16-byte aligned");
+  // (the slot count is checked below, once the tile shape is known)
   p.hw_out = (long long)a->H * a->W;
   if (a->up_phase) {
     MDX_CHECK_ARG(a->up_phase >= 1 && a->up_phase <= 4 && a->nseg == 1 && a->seg_taps[0] == 4 && !a->geglu,

@@ -63,6 +63,8 @@ struct GnP {
   void* out; long long ldo;
   void* raw; long long ldraw;  // optional un-normalised copy of concat(x1, x2) in the out dtype
   double* stats;
+  const float* chan1; const float* chan2;  // optional per-image [slots][2][C] partial {sums | sums of squares}
+  int slots1, slots2;                      // written by the producers (mdx_gemm_args.chan_stats)
   const float* ss; long long ldss;  // optional FiLM rows [n][scale(C) | shift(C)]: y = gn(x) * (1 + scale) + shift
 };
 
@@ -215,6 +217,50 @@ __global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
   }
 }
 
+// Partial sums written by the producing GEMMs' epilogues (mdx_gemm_args.chan_stats: per image [slots][2][C], one slot
+// per 32 output rows) -> per-group sums.  One warp per (image, group), fixed summation order (deterministic); a group
+// of concat(x1, x2) may take channels from both tensors.
+__global__ void __launch_bounds__(128) gn_fold_kernel(const GnP p) {
+  __shared__ double red[2][4];
+  const int i = blockIdx.x;                       // (image, group)
+  const int img = i / p.groups, g = i % p.groups;
+  const int c_lo = g * p.cpg;
+  // items = (slot, channel of the group); a thread walks them with stride 128, four loads in flight
+  float fs[4] = {0.f, 0.f, 0.f, 0.f}, fq[4] = {0.f, 0.f, 0.f, 0.f};
+  auto item = [&](int it, float& s, float& q) {
+    const int c = c_lo + it % p.cpg;
+    const bool first = c < p.C1;
+    const int C = first ? p.C1 : p.C2, cc = first ? c : c - p.C1, slots = first ? p.slots1 : p.slots2;
+    const int k = it / p.cpg;
+    if (k < slots) {
+      const float* src = (first ? p.chan1 : p.chan2) + ((long long)img * slots + k) * 2 * C + cc;
+      s += src[0];
+      q += src[C];
+    }
+  };
+  const int slots_max = p.slots1 > p.slots2 ? p.slots1 : p.slots2;
+  const int total = slots_max * p.cpg;
+  int it = threadIdx.x;
+  for (; it + 3 * 128 < total; it += 4 * 128) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) item(it + u * 128, fs[u], fq[u]);
+  }
+  for (; it < total; it += 128) item(it, fs[0], fq[0]);
+  double s = ((double)fs[0] + fs[1]) + ((double)fs[2] + fs[3]);
+  double q = ((double)fq[0] + fq[1]) + ((double)fq[2] + fq[3]);
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, m);
+    q += __shfl_xor_sync(0xffffffffu, q, m);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    p.stats[(long long)i * 2] = (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]);
+    p.stats[(long long)i * 2 + 1] = (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]);
+  }
+}
+
 // ---------------- LayerNorm: one warp per R rows, rows held in registers ----------------
 template <typename T> __device__ __forceinline__ float4 ln_ld4(const T* p);
 template <> __device__ __forceinline__ float4 ln_ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -309,8 +355,12 @@ int launch_gn(GnP p, cudaStream_t st) {
   p.rows_per_block = (p.HW + chunks - 1) / chunks;
   chunks = (p.HW + p.rows_per_block - 1) / p.rows_per_block;
   dim3 grid(chunks, p.n), block(p.CV * p.RP);
-  MDX_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, sizeof(double) * 2 * p.groups * p.n, st));
-  gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
+  if (p.chan1) {
+    gn_fold_kernel<<<p.n * p.groups, 128, 0, st>>>(p);
+  } else {
+    MDX_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, sizeof(double) * 2 * p.groups * p.n, st));
+    gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
+  }
   MDX_CHECK_LAUNCH();
   gn_apply_kernel<T, TO><<<grid, block, 0, st>>>(p);
   MDX_CHECK_LAUNCH();
@@ -353,7 +403,8 @@ int launch_ln(const void* x, long long ldx, int rows, int C, float eps, const fl
 static int gn_run(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64_t ld2, int32_t C2, int32_t n,
                   int32_t HW, int32_t groups, float eps, const float* gamma, const float* beta, int32_t silu,
                   void* out, int64_t ldo, void* raw_copy, int64_t ldraw, int32_t in_dtype, int32_t out_dtype,
-                  const float* scale_shift, int64_t ld_ss, double* stats_scratch, void* stream) {
+                  const float* scale_shift, int64_t ld_ss, double* stats_scratch, void* stream,
+                  const float* chan1 = nullptr, int slots1 = 0, const float* chan2 = nullptr, int slots2 = 0) {
   MDX_CHECK_ARG(x1 && out && gamma && beta && stats_scratch, "mdx_groupnorm: NULL operand");
   MDX_CHECK_ARG(n > 0 && HW > 0 && C1 > 0 && C2 >= 0, "mdx_groupnorm: empty problem");
   MDX_CHECK_ARG(C2 == 0 || x2 != nullptr, "mdx_groupnorm: x2 is NULL but C2 > 0");
@@ -374,6 +425,7 @@ static int gn_run(const void* x1, int64_t ld1, int32_t C1, const void* x2, int64
   p.eps = eps; p.gamma = gamma; p.beta = beta; p.silu = silu; p.out = out; p.ldo = ldo;
   p.raw = raw_copy; p.ldraw = ldraw; p.stats = stats_scratch;
   p.ss = scale_shift; p.ldss = ld_ss;
+  p.chan1 = chan1; p.chan2 = chan2; p.slots1 = slots1; p.slots2 = slots2;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (in_dtype == MDX_BF16) return launch_gn<bf16, bf16>(p, st);
   if (out_dtype == MDX_BF16) return launch_gn<float, bf16>(p, st);
@@ -395,6 +447,18 @@ extern "C" int mdx_groupnorm_film(const void* x, int64_t ldx, int32_t C, int32_t
   MDX_CHECK_ARG(scale_shift && ld_ss >= 2 * (int64_t)C, "mdx_groupnorm_film: scale_shift rows must hold 2*C floats");
   return gn_run(x, ldx, C, nullptr, 0, 0, n, HW, groups, eps, gamma, beta, silu, out, ldo, nullptr, 0, in_dtype,
                 out_dtype, scale_shift, ld_ss, stats_scratch, stream);
+}
+
+extern "C" int mdx_groupnorm_pre(const void* x1, int64_t ld1, int32_t C1, const float* chan1, int32_t slots1,
+                                 const void* x2, int64_t ld2, int32_t C2, const float* chan2, int32_t slots2, int32_t n, int32_t HW, int32_t groups,
+                                 float eps, const float* gamma, const float* beta, const float* scale_shift,
+                                 int64_t ld_ss, int32_t silu, void* out, int64_t ldo, void* raw_copy, int64_t ldraw,
+                                 int32_t in_dtype, int32_t out_dtype, double* stats_scratch, void* stream) {
+  MDX_CHECK_ARG(chan1 != nullptr && slots1 > 0 && (C2 == 0 || (chan2 != nullptr && slots2 > 0)),
+                "mdx_groupnorm_pre: every source needs its channel statistics");
+  MDX_CHECK_ARG(scale_shift == nullptr || ld_ss >= 2 * (int64_t)(C1 + C2), "mdx_groupnorm_pre: scale_shift rows too short");
+  return gn_run(x1, ld1, C1, x2, ld2, C2, n, HW, groups, eps, gamma, beta, silu, out, ldo, raw_copy, ldraw, in_dtype,
+                out_dtype, scale_shift, ld_ss, stats_scratch, stream, chan1, slots1, chan2, slots2);
 }
 
 extern "C" int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps, const float* gamma,

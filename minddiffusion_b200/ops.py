@@ -55,6 +55,11 @@ def _f32(t, name):
     return t
 
 
+def stat_slots(n_img, H, W, up=False):
+    """Statistics slots per image of gemm_tc(chan_stats=...) for an [n_img, H, W, *] operand (0: unsupported)."""
+    return int(_lib.load().mdx_gemm_tc_stat_slots(n_img, H, W, int(up)))
+
+
 def pick_block_n(N, geglu=False):
     return int(_lib.load().mdx_gemm_tc_pick_block_n(N, 1 if geglu else 0))
 
@@ -63,7 +68,7 @@ ACT = {None: 0, "gelu": 1, "quick_gelu": 2}
 
 
 def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
-            block_n=0, act=None, up_phase=0):
+            block_n=0, act=None, up_phase=0, chan_stats=None):
     """Tensor-core implicit GEMM (mdx_gemm_tc).
 
     segs: list of (a, taps); a is bf16 ``[n, H, W, C]`` (conv view) or ``[M, C]`` (dense), taps 9 or 1.
@@ -125,6 +130,12 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
     args.block_n = block_n
     args.act = ACT[act]
     args.up_phase = up_phase
+    if chan_stats is not None:
+        slots = stat_slots(n_img, H, W, bool(up_phase))
+        if slots == 0 or chan_stats.dtype != torch.float32 or not chan_stats.is_contiguous() or (
+                tuple(chan_stats.shape) != (n_img, slots, 2, n_out)):
+            raise ValueError("chan_stats must be contiguous float32 [n_img, %d, 2, %d]" % (slots, n_out))
+        args.chan_stats = chan_stats.data_ptr()
     if GEMM_TC_PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -182,7 +193,7 @@ def conv_direct(x, w, kh=1, kw=1, stride=1, pad=0, upsample=False, pre_silu=Fals
 
 
 def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=None, scratch=None, out_dtype=None,
-              raw_copy=False):
+              raw_copy=False, chan1=None, chan2=None):
     """GroupNorm(+SiLU) over NHWC ``[n, H, W, C]`` (optionally over concat(x1, x2) along C).
     out_dtype: dtype of the result (default: dtype of x1).  raw_copy=True also returns the un-normalised
     concat(x1, x2) converted to out_dtype (second return value)."""
@@ -206,6 +217,14 @@ def groupnorm(x1, gamma, beta, groups=32, eps=1e-5, silu=False, x2=None, out=Non
         scratch = torch.empty(n * groups * 2, dtype=torch.float64, device=x1.device)
     elif scratch.dtype != torch.float64 or scratch.numel() < n * groups * 2:
         raise ValueError("scratch must hold n*groups*2 float64")
+    if chan1 is not None and (x2 is None or chan2 is not None):
+        # statistics were accumulated by the producers' GEMM epilogues: no pass over the activation
+        check(lib.mdx_groupnorm_pre(_p(x1), ld1, C1, _p(chan1), chan1.shape[1], _p(x2), ld2, C2, _p(chan2),
+                                    chan2.shape[1] if chan2 is not None else 0, n, HW, groups, float(eps),
+                                    _p(_f32(gamma, "gamma")), _p(_f32(beta, "beta")), None, 0, int(silu), _p(out), ldo,
+                                    _p(raw), C1 + C2 if raw_copy else 0, _dt(x1), _dt(out), _p(scratch), _stream()),
+              "mdx_groupnorm_pre")
+        return (out, raw) if raw_copy else out
     check(lib.mdx_groupnorm(_p(x1), ld1, C1, _p(x2), ld2, C2, n, HW, groups, float(eps), _p(_f32(gamma, "gamma")),
                             _p(_f32(beta, "beta")), int(silu), _p(out), ldo, _p(raw), C1 + C2 if raw_copy else 0,
                             _dt(x1), _dt(out), _p(scratch), _stream()), "mdx_groupnorm")

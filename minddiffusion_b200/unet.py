@@ -18,6 +18,8 @@ openaimodel.py:245-576; wukong-huahua's copy takes the SD-v1 constructor argumen
 dtype=torch.bfloat16 is the product path; dtype=torch.float32 is the "check mode" of the north star: the same
 graph on CUDA-core fp32 kernels, used to separate orchestration errors from bf16 rounding.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -228,15 +230,26 @@ class UNetModel:
     # ------------------------------------------------------------------------------------------------
     # op helpers (bf16 tensor-core path / fp32 check path)
     # ------------------------------------------------------------------------------------------------
-    def _conv3(self, x, w, b, rowbias=None, residual=None, skips=None, trunk=False):
+    def _chan(self, n, H, W, C, up=False):
+        """[n, slots, 2, C] fp32 buffer a GEMM epilogue fills with partial per-channel sums / sums of squares of its
+        output (one slot per 32 rows): the GroupNorm that reads the tensor next needs no statistics pass
+        (mdx_groupnorm_pre).  None for images below 128 pixels (two-pass GroupNorm there)."""
+        if os.environ.get("MDX_NO_EPI_STATS"):   # A/B switch: two-pass GroupNorm everywhere
+            return None
+        slots = ops.stat_slots(n, H, W, up)
+        return torch.empty((n, slots, 2, C), dtype=torch.float32, device=self.device) if slots else None
+
+    def _conv3(self, x, w, b, rowbias=None, residual=None, skips=None, trunk=False, stats=False):
         """3x3 stride-1 conv on NHWC x; `skips`: raw bf16 tensors whose fused 1x1 conv is K-concatenated (bf16
-        mode); trunk=True writes the fp32 residual stream."""
+        mode); trunk=True writes the fp32 residual stream; stats=True tags the result with its channel statistics."""
         n, H, W, _ = x.shape
         if self.bf16:
             segs = [(x, 9)] + [(s, 1) for s in (skips or [])]
-            out = ops.gemm_tc(segs, w, bias=b, rowbias=rowbias, residual=residual,
-                              out_dtype=torch.float32 if trunk else torch.bfloat16)
-            return out.view(n, H, W, -1)
+            chan = self._chan(n, H, W, w.shape[0]) if stats else None
+            out = ops.gemm_tc(segs, w, bias=b, rowbias=rowbias, residual=residual, chan_stats=chan,
+                              out_dtype=torch.float32 if trunk else torch.bfloat16).view(n, H, W, -1)
+            out._mdx_chan = chan
+            return out
         return ops.conv_direct(x, w, 3, 3, 1, 1, bias=b, rowbias=rowbias, residual=residual)
 
     def _linear(self, x, w, b=None, residual=None, geglu_bn=None, out=None, trunk=False):
@@ -264,20 +277,23 @@ class UNetModel:
         g1, b1 = L[pre + "n1"]
         w2, bb2, has_skip = L[pre + "c2"]
         raw = None
+        ch1 = getattr(x1, "_mdx_chan", None)
+        ch2 = getattr(x2, "_mdx_chan", None) if x2 is not None else None
         if self.bf16 and has_skip:  # the same pass also emits the bf16 operand of the 1x1 skip conv
             h, raw = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch,
-                                   out_dtype=self.dtype, raw_copy=True)
+                                   out_dtype=self.dtype, raw_copy=True, chan1=ch1, chan2=ch2)
         else:
-            h = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch, out_dtype=self.dtype)
+            h = ops.groupnorm(x1, g1, b1, 32, 1e-5, silu=True, x2=x2, scratch=self._gn_scratch, out_dtype=self.dtype,
+                              chan1=ch1, chan2=ch2)
         w1, bb1 = L[pre + "c1"]
         off, _ = L[pre + "emb"]
-        h = self._conv3(h, w1, bb1, rowbias=emb_all[:, off:off + cout])
+        h = self._conv3(h, w1, bb1, rowbias=emb_all[:, off:off + cout], stats=True)
         g2, b2 = L[pre + "n2"]
-        h = ops.groupnorm(h, g2, b2, 32, 1e-5, silu=True, scratch=self._gn_scratch)
+        h = ops.groupnorm(h, g2, b2, 32, 1e-5, silu=True, scratch=self._gn_scratch, chan1=getattr(h, "_mdx_chan", None))
         if not has_skip:
-            return self._conv3(h, w2, bb2, residual=x1, trunk=True)
+            return self._conv3(h, w2, bb2, residual=x1, trunk=True, stats=True)
         if self.bf16:
-            return self._conv3(h, w2, bb2, skips=[raw], trunk=True)
+            return self._conv3(h, w2, bb2, skips=[raw], trunk=True, stats=True)
         xin = x1 if x2 is None else ops.concat_channels(x1, x2)
         ws, bs = L[pre + "skip"]
         sk = ops.conv_direct(xin, ws, bias=bs)
@@ -291,7 +307,8 @@ class UNetModel:
         scale = dh ** -0.5
         dt = self.dtype
         gn, bn_ = L[pre + "norm"]
-        hn = ops.groupnorm(x, gn, bn_, 32, 1e-6, silu=False, scratch=self._gn_scratch, out_dtype=dt)
+        hn = ops.groupnorm(x, gn, bn_, 32, 1e-6, silu=False, scratch=self._gn_scratch, out_dtype=dt,
+                           chan1=getattr(x, "_mdx_chan", None))
         w, b = L[pre + "proj_in"]
         t = self._linear(hn, w, b, trunk=True)           # [n*N, C] token stream
         C = t.shape[-1]
@@ -315,6 +332,12 @@ class UNetModel:
             # the last block's output only feeds proj_out as a GEMM operand: store it in the operand dtype
             t = self._linear(gg, *L[tb + "ff2"], residual=t, trunk=(d != self.depth - 1))
         w, b = L[pre + "proj_out"]
+        if self.bf16:  # as a 1x1 conv over [n, H, W, C] so that the epilogue knows each row's image
+            chan = self._chan(n, H, W, ch)
+            out = ops.gemm_tc([(t.view(n, H, W, C), 1)], w, bias=b, residual=x.view(n * N, ch), chan_stats=chan,
+                              out_dtype=torch.float32).view(n, H, W, ch)
+            out._mdx_chan = chan
+            return out
         return self._linear(t, w, b, residual=x, trunk=True).view(n, H, W, ch)
 
     def _down(self, pre, x):
@@ -323,13 +346,19 @@ class UNetModel:
         if self.bf16:
             col = ops.im2col3x3(x, 2, out_dtype=self.dtype)      # [n, OH, OW, 9C]
             OH, OW = col.shape[1], col.shape[2]
-            return ops.gemm_tc([(col.view(-1, 9 * C), 1)], w, bias=b, out_dtype=torch.float32).view(n, OH, OW, -1)
+            chan = self._chan(n, OH, OW, w.shape[0])
+            out = ops.gemm_tc([(col, 1)], w, bias=b, out_dtype=torch.float32, chan_stats=chan).view(n, OH, OW, -1)
+            out._mdx_chan = chan
+            return out
         return ops.conv_direct(x, w, 3, 3, 2, 1, bias=b)
 
     def _up(self, pre, x):
         w, b = self.L[pre + "up"]
         if self.bf16:
-            return upsample_conv3x3(ops.cast(x, self.dtype), w, b, torch.float32)
+            chan = self._chan(x.shape[0], x.shape[1], x.shape[2], w[0].shape[0], up=True)
+            out = upsample_conv3x3(ops.cast(x, self.dtype), w, b, torch.float32, chan)
+            out._mdx_chan = chan
+            return out
         return ops.conv_direct(x, w, 3, 3, 1, 1, upsample=True, bias=b)
 
     # ------------------------------------------------------------------------------------------------
@@ -386,7 +415,7 @@ class UNetModel:
         def run(pre, layer, h, skip):
             kind = layer[0]
             if kind == "conv":
-                return self._conv3(h, *L[pre + "conv"], trunk=True)
+                return self._conv3(h, *L[pre + "conv"], trunk=True, stats=True)
             if kind == "res":
                 return self._res(pre, layer, h, skip, emb_all)
             if kind == "st":
@@ -412,7 +441,8 @@ class UNetModel:
             if taps is not None:
                 taps["output_blocks.%d" % bi] = h
         g, b = L["out_norm"]
-        h = ops.groupnorm(h, g, b, 32, 1e-5, silu=True, scratch=self._gn_scratch, out_dtype=self.dtype)
+        h = ops.groupnorm(h, g, b, 32, 1e-5, silu=True, scratch=self._gn_scratch, out_dtype=self.dtype,
+                          chan1=getattr(h, "_mdx_chan", None))
         nn_, H, W, _ = h.shape
         w, b = L["out_conv"]
         if self.bf16:
@@ -485,12 +515,12 @@ def fold_upsample_weights(w):
     return out
 
 
-def upsample_conv3x3(x, phase_weights, bias, out_dtype):
+def upsample_conv3x3(x, phase_weights, bias, out_dtype, chan_stats=None):
     """x: bf16 NHWC [n, H, W, C] -> conv3x3(nearest_x2(x)) as [n, 2H, 2W, Cout], four mdx_gemm_tc launches."""
     n, H, W, _ = x.shape
     out = torch.empty((n, 2 * H, 2 * W, phase_weights[0].shape[0]), dtype=out_dtype, device=x.device)
     for ph, wp in enumerate(phase_weights):
-        ops.gemm_tc([(x, 4)], wp, out=out.view(n * 4 * H * W, -1), bias=bias, up_phase=ph + 1)
+        ops.gemm_tc([(x, 4)], wp, out=out.view(n * 4 * H * W, -1), bias=bias, up_phase=ph + 1, chan_stats=chan_stats)
     return out
 
 

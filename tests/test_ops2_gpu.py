@@ -167,3 +167,47 @@ def test_single_tile_attention_kernel(B, heads, Nq, Nk):
     scale = float(ref.abs().max())
     assert float((out.float().cpu() - ref).abs().max()) / scale < 2e-2
     assert float((out.float() - out_general.float()).abs().max()) / scale < 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,H,W,Cin,C1,C2", [(3, 16, 16, 64, 320, 0), (2, 16, 8, 128, 640, 320), (2, 48, 40, 64, 64, 64),
+                                              (2, 32, 32, 64, 160, 0)])
+def test_groupnorm_from_epilogue_statistics(n, H, W, Cin, C1, C2):
+    """The GEMM epilogue stores, per 32 output rows, the per-channel sums / sums of squares of what it wrote
+    (chan_stats); mdx_groupnorm_pre folds them into group statistics.  Result must equal the two-pass GroupNorm of
+    the same tensors (also for a concat whose groups straddle the two sources and for ragged tiles), and two runs
+    must agree bit for bit (no atomics)."""
+    from minddiffusion_b200 import ops
+    g = torch.Generator().manual_seed(n + C1 + C2)
+    slots = ops.stat_slots(n, H, W)
+    assert slots > 0 and ops.stat_slots(4, 8, 8) == 0
+    outs, chans = [], []
+    for C in [c for c in (C1, C2) if c]:
+        x = torch.randn(n, H, W, Cin, generator=g).bfloat16().cuda()
+        w = (torch.randn(C, 9 * Cin, generator=g) / (9 * Cin) ** 0.5).bfloat16().cuda()
+        res = torch.randn(n * H * W, C, generator=g).cuda()
+        b = torch.randn(C, generator=g).cuda()
+        chan = torch.full((n, slots, 2, C), float("nan"), device="cuda")
+        o = ops.gemm_tc([(x, 9)], w, bias=b, residual=res, out_dtype=torch.float32, chan_stats=chan).view(n, H, W, C)
+        ref = torch.stack((o.double().sum((1, 2)), (o.double() ** 2).sum((1, 2))), dim=1)
+        assert torch.allclose(chan.double().sum(1), ref, rtol=1e-4, atol=1e-2)
+        chan_b = torch.empty_like(chan)
+        ops.gemm_tc([(x, 9)], w, bias=b, residual=res, out_dtype=torch.float32, chan_stats=chan_b)
+        assert torch.equal(chan, chan_b)
+        outs.append(o)
+        chans.append(chan)
+    C = C1 + C2
+    gamma, beta = torch.randn(C, generator=g).cuda(), torch.randn(C, generator=g).cuda()
+    x2, c2 = (outs[1], chans[1]) if C2 else (None, None)
+    two_pass = ops.groupnorm(outs[0], gamma, beta, 32, 1e-5, silu=True, x2=x2, out_dtype=torch.bfloat16)
+    fused = ops.groupnorm(outs[0], gamma, beta, 32, 1e-5, silu=True, x2=x2, out_dtype=torch.bfloat16, chan1=chans[0],
+                          chan2=c2)
+    assert float((two_pass.float() - fused.float()).abs().max()) <= 2e-2 * float(two_pass.float().abs().max())
+    assert float((two_pass.float() - fused.float()).abs().mean()) < 1e-4
+    # bf16 output: statistics are those of the rounded values
+    chan = torch.empty(n, slots, 2, C1, device="cuda")
+    x = torch.randn(n, H, W, Cin, generator=g).bfloat16().cuda()
+    w = (torch.randn(C1, 9 * Cin, generator=g) / (9 * Cin) ** 0.5).bfloat16().cuda()
+    o = ops.gemm_tc([(x, 9)], w, chan_stats=chan).view(n, H, W, C1)
+    ref = torch.stack((o.double().sum((1, 2)), (o.double() ** 2).sum((1, 2))), dim=1)
+    assert torch.allclose(chan.double().sum(1), ref, rtol=1e-4, atol=1e-2)
