@@ -70,6 +70,46 @@ __device__ __forceinline__ float gelu_tanh_fast(float x) {
   return x * r;
 }
 
+// Packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot for two lanes of elementwise epilogue math.
+__device__ __forceinline__ void ffma2v(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void fmul2v(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmul.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void fadd2v(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tadd.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+// GEGLU on a pair: (v + bv) * gelu_tanh(g + bg), with gelu(x) = x / (1 + 2^(x (c1 + c3 x^2))), c1 = -2 log2(e) k0,
+// c3 = c1 k1 (the constants of gelu_tanh_fast folded): 8 packed FP ops + 4 MUFU for two outputs.
+__device__ __forceinline__ void geglu_pair(float& o0, float& o1, float v0, float v1, float g0, float g1, float bv0,
+                                           float bv1, float bg0, float bg1) {
+  const float c1 = -2.3022082f, c3 = -0.10294324f;
+  float t0, t1, w0, w1, a0, a1, d0, d1;
+  fadd2v(g0, g1, g0, g1, bg0, bg1);
+  fadd2v(v0, v1, v0, v1, bv0, bv1);
+  fmul2v(t0, t1, g0, g1, g0, g1);
+  ffma2v(w0, w1, t0, t1, c3, c3, c1, c1);
+  fmul2v(a0, a1, g0, g1, w0, w1);
+  float e0, e1, r0, r1;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  fadd2v(d0, d1, e0, e1, 1.f, 1.f);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(d1));
+  fmul2v(g0, g1, g0, g1, r0, r1);
+  fmul2v(o0, o1, v0, v1, g0, g1);
+}
+
 // epilogue activations: 1 = GELU (tanh form), 2 = QuickGELU x * sigmoid(1.702 x)
 __device__ __forceinline__ float apply_act(float x, int act) {
   if (act == 1) return gelu_tanh_fast(x);

@@ -474,10 +474,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
               const uint4 ubv = lds128(stg + 2560 + 16 * j), ubg = lds128(stg + 2688 + 16 * j);
               const float4 bv = make_float4(__uint_as_float(ubv.x), __uint_as_float(ubv.y), __uint_as_float(ubv.z), __uint_as_float(ubv.w));
               const float4 bg = make_float4(__uint_as_float(ubg.x), __uint_as_float(ubg.y), __uint_as_float(ubg.z), __uint_as_float(ubg.w));
-              const float o0 = (__uint_as_float(rv[4 * j]) + bv.x) * gelu_tanh_fast(__uint_as_float(rg[4 * j]) + bg.x);
-              const float o1 = (__uint_as_float(rv[4 * j + 1]) + bv.y) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 1]) + bg.y);
-              const float o2 = (__uint_as_float(rv[4 * j + 2]) + bv.z) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 2]) + bg.z);
-              const float o3 = (__uint_as_float(rv[4 * j + 3]) + bv.w) * gelu_tanh_fast(__uint_as_float(rg[4 * j + 3]) + bg.w);
+              float o0, o1, o2, o3;
+              geglu_pair(o0, o1, __uint_as_float(rv[4 * j]), __uint_as_float(rv[4 * j + 1]), __uint_as_float(rg[4 * j]),
+                         __uint_as_float(rg[4 * j + 1]), bv.x, bv.y, bg.x, bg.y);
+              geglu_pair(o2, o3, __uint_as_float(rv[4 * j + 2]), __uint_as_float(rv[4 * j + 3]),
+                         __uint_as_float(rg[4 * j + 2]), __uint_as_float(rg[4 * j + 3]), bv.z, bv.w, bg.z, bg.w);
               pk[2 * j] = pack_bf16x2(o0, o1);
               pk[2 * j + 1] = pack_bf16x2(o2, o3);
             } else {
