@@ -25,7 +25,7 @@ import numpy as np
 import torch
 
 from . import _lib, ops
-from .unet import _t
+from .unet import _t, fold_upsample_weights, upsample_conv3x3
 
 
 # -------------------------------------------------------------------------------------------------------------
@@ -375,7 +375,12 @@ class Text2ImUNet:
             elif layer[0] == "res":
                 cin, cout, ud = layer[1], layer[2], layer[3]
                 L[pre + "n1"] = (g(pre + "in_layers_0.gamma"), g(pre + "in_layers_0.beta"))
-                L[pre + "c1"] = (self._w(conv_k(g(pre + "in_layers_2.conv.weight"))), g(pre + "in_layers_2.conv.bias"))
+                if ud == "up" and self.bf16:  # nearest x2 + conv3x3 as four 2x2 phase GEMMs over the source image
+                    L[pre + "c1"] = ([self._w(wp) for wp in fold_upsample_weights(g(pre + "in_layers_2.conv.weight"))],
+                                     g(pre + "in_layers_2.conv.bias"))
+                else:
+                    L[pre + "c1"] = (self._w(conv_k(g(pre + "in_layers_2.conv.weight"))),
+                                     g(pre + "in_layers_2.conv.bias"))
                 emb_w.append(g(pre + "emb_layers.1.weight"))
                 emb_b.append(g(pre + "emb_layers.1.bias"))
                 L[pre + "emb"] = off
@@ -539,8 +544,13 @@ class Text2ImUNet:
         if ud == "down":       # h_upd / x_upd = AvgPool2d(2, 2) (unet.py:139-141)
             h, x = ops.avgpool2x2(h), ops.avgpool2x2(x1)
         elif ud == "up":       # nearest x2, no conv (unet.py:49-52, 136-138)
-            h, x = ops.upsample_nearest2x(h), ops.upsample_nearest2x(x1)
-        h = self._conv3(h, *L[pre + "c1"])
+            x = ops.upsample_nearest2x(x1)
+            if not self.bf16:
+                h = ops.upsample_nearest2x(h)
+        if ud == "up" and self.bf16:
+            h = upsample_conv3x3(h, L[pre + "c1"][0], L[pre + "c1"][1], self.dtype)
+        else:
+            h = self._conv3(h, *L[pre + "c1"])
         off = L[pre + "emb"]
         g2, b2 = L[pre + "n2"]
         h = ops.groupnorm_film(h, g2, b2, emb_all[:, off:off + 2 * cout], 32, 1e-5, silu=True,
@@ -608,10 +618,12 @@ class Text2ImUNet:
         w, b = L["out_conv"]
         return self._conv3(h, w, b, trunk=True)
 
-    def forward_nhwc(self, x_nchw, timesteps, repeat=1, taps=None):
+    def forward_nhwc(self, x_nchw, timesteps, repeat=1, taps=None, random_prompt=None):
         """x_nchw: fp32 [B, 3, H, W], read `repeat` times (2 = CombinePrompt's concat((half, half)), guider.py:32-35);
         timesteps: [B*repeat] mapped timesteps.  Text operands must have been set for B*repeat images.  Returns fp32
-        NHWC [B*repeat, H, W, ld >= out_channels]."""
+        NHWC [B*repeat, H, W, ld >= out_channels].
+        random_prompt = (token_row, mask_row, lo, hi): run set_random_prompt for images [lo, hi) first — inside the
+        same captured graph when graphs are on, so that a guided step is ONE graph launch."""
         n = x_nchw.shape[0] * repeat
         if self._n != n:
             raise RuntimeError("text operands are set for %d images, forward has %d (call set_prompt)" % (self._n, n))
@@ -621,23 +633,39 @@ class Text2ImUNet:
         t = timesteps.to(device=self.device, dtype=torch.float32).contiguous()
         if t.numel() != n:
             raise ValueError("timesteps must have %d entries" % n)
+        if random_prompt is not None:
+            tok, msk, lo, hi = random_prompt
+            tok = tok.to(device=self.device, dtype=torch.int32).contiguous()
+            msk = (torch.ones_like(tok) if msk is None else msk.to(device=self.device, dtype=torch.int32)).contiguous()
         if not self.use_cuda_graph or taps is not None:
+            if random_prompt is not None:
+                self.set_random_prompt(tok, msk, lo, hi)
             return self._forward_impl(x_nchw, t, repeat, taps)
-        key = (tuple(x_nchw.shape), repeat)
+        key = (tuple(x_nchw.shape), repeat, None if random_prompt is None else (lo, hi))
         ent = self._graphs.get(key)
         if ent is None:
             sx, st_ = x_nchw.clone(), t.clone()
-            self._forward_impl(sx, st_, repeat)
+            stok, smsk = (tok.clone(), msk.clone()) if random_prompt is not None else (None, None)
+
+            def body():
+                if stok is not None:
+                    self.set_random_prompt(stok, smsk, lo, hi)
+                return self._forward_impl(sx, st_, repeat)
+
+            body()
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
-                sout = self._forward_impl(sx, st_, repeat)
-            ent = (graph, sx, st_, sout, _lib.launch_count() - n0)
+                sout = body()
+            ent = (graph, sx, st_, stok, smsk, sout, _lib.launch_count() - n0)
             self._graphs[key] = ent
-        graph, sx, st_, sout, nk = ent
+        graph, sx, st_, stok, smsk, sout, nk = ent
         sx.copy_(x_nchw)
         st_.copy_(t)
+        if stok is not None:
+            stok.copy_(tok)
+            smsk.copy_(msk)
         graph.replay()
         self.replayed_launches += nk
         return sout
@@ -722,9 +750,8 @@ class GenerativePSampleDiffusionModel(_DiffusionBase):
     def step(self, x, i, random_token, random_mask=None, noise=None):
         """One guided ancestral step on x [P, 3, S, S]; returns (x_prev, pred_xstart)."""
         P, m = self.P, self.model
-        m.set_random_prompt(random_token, random_mask, P, 2 * P)
         t = self.tmap[i].expand(2 * P)
-        out = m.forward_nhwc(x, t, repeat=2)
+        out = m.forward_nhwc(x, t, repeat=2, random_prompt=(random_token, random_mask, P, 2 * P))
         if noise is None and i != 0:
             noise = torch.randn(x.shape, dtype=torch.float32, device=self.device)
         x0 = torch.empty_like(x)
