@@ -282,7 +282,9 @@ int mdx_sampler_dpmpp2m_step(const void* eps_model, int64_t ld_eps, int32_t mode
  * mdx_resize_bilinear — ops.ResizeBilinear(size, align_corners=False) (text2im_model.py:166,191) on fp32 NCHW;
  *      quantize_u8 != 0 first applies PMeanVariance.superResPreprocess (gaussian_diffusion.py:224-230):
  *      round((v + 1) * 127.5) / 127.5 - 1 to every source pixel.
- * mdx_nchw2_to_nhwc_pad — mdx_nchw_to_nhwc_pad over ops.Concat(axis=1)((x1, x2)) (text2im_model.py:192).
+ * mdx_nchw2_to_nhwc_pad — mdx_nchw_to_nhwc_pad over ops.Concat(axis=1)((x1, x2)) (text2im_model.py:192; the
+ *      'hybrid' / 'concat' DiffusionWrapper of wukong-huahua ddpm.py:363-372).  x1 has n images, read `repeat` times;
+ *      x2 has n2 = n (same) or n2 = n*repeat images (one per output image: the [uncond | cond] c_concat).
  * mdx_sampler_glide_step — Guider + PMeanVariance + PSample / DDimSample in one pass
  *      (guider.py:60-70, gaussian_diffusion.py:158-181, :49-63, :82-103).
  *      model_out: NHWC [cfg ? 2P : P, h, w, >= 2C]: channels [0,C) eps, [C,2C) variance fraction v; rows [0,P) are
@@ -310,8 +312,8 @@ int mdx_embedding_masked(const float* table, int32_t vocab, int32_t width, const
                          void* stream);
 int mdx_resize_bilinear(const float* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t OH, int32_t OW,
                         int32_t quantize_u8, float* out, void* stream);
-int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t C2, int32_t n, int32_t H, int32_t W,
-                          int32_t repeat, int32_t Cpad, void* out, int32_t dtype, void* stream);
+int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t C2, int32_t n, int32_t n2, int32_t H,
+                          int32_t W, int32_t repeat, int32_t Cpad, void* out, int32_t dtype, void* stream);
 int mdx_sampler_glide_step(const void* model_out, int64_t ld_out, int32_t model_dtype, int32_t cfg, float scale,
                            int32_t mode, const float* x, const float* coef_host, const float* noise, float* x_prev,
                            float* pred_xstart, int32_t P, int32_t C, int32_t h, int32_t w, void* stream);

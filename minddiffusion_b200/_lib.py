@@ -99,7 +99,8 @@ SIGNATURES = {
     "mdx_copy_rows": (c_int, [c_p, c_i64, c_i64, c_p, c_i64, c_i64, c_int, c_int, c_i64, c_p]),
     "mdx_embedding_masked": (c_int, [c_p, c_int, c_int, c_p, c_p, c_int, c_p, c_p, c_int, c_p, c_int, c_p]),
     "mdx_resize_bilinear": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_p]),
-    "mdx_nchw2_to_nhwc_pad": (c_int, [c_p, c_int, c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_int, c_p]),
+    "mdx_nchw2_to_nhwc_pad": (c_int, [c_p, c_int, c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_int,
+                                      c_p]),
     "mdx_sampler_glide_step": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_int, c_p, c_p, c_p, c_p, c_p, c_int, c_int,
                                        c_int, c_int, c_p]),
 }

@@ -103,20 +103,22 @@ __global__ void resize_bilinear_kernel(const float* __restrict__ x, int nc, int 
   }
 }
 
-// NHWC (padded) image of concat(x1, x2) along channels; x2 may be NULL.  Both sources are read `repeat` times.
+// NHWC (padded) image of concat(x1, x2) along channels; x2 may be NULL.  x1 [n] is read `repeat` times; x2 holds n2
+// images (n: read `repeat` times as well; n*repeat: one per output image, e.g. [uncond | cond] concat conditioning).
 template <typename T>
 __global__ void nchw2_to_nhwc_kernel(const float* __restrict__ x1, int C1, const float* __restrict__ x2, int C2, int n,
-                                     int H, int W, int repeat, int Cpad, T* __restrict__ out) {
+                                     int n2, int H, int W, int repeat, int Cpad, T* __restrict__ out) {
   const long long HW = (long long)H * W;
   const long long total = (long long)n * repeat * HW * Cpad;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % Cpad);
     const long long pix = i / Cpad;
     const long long hw = pix % HW;
-    const int b = (int)(pix / HW) % n;
+    const int bb = (int)(pix / HW);
+    const int b = bb % n;
     float v = 0.f;
     if (c < C1) v = x1[((long long)b * C1 + c) * HW + hw];
-    else if (c < C1 + C2) v = x2[((long long)b * C2 + (c - C1)) * HW + hw];
+    else if (c < C1 + C2) v = x2[((long long)(bb % n2) * C2 + (c - C1)) * HW + hw];
     out[i] = from_f32<T>(v);
   }
 }
@@ -241,17 +243,19 @@ extern "C" int mdx_resize_bilinear(const float* x, int32_t n, int32_t C, int32_t
   return MDX_OK;
 }
 
-extern "C" int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t C2, int32_t n, int32_t H,
-                                     int32_t W, int32_t repeat, int32_t Cpad, void* out, int32_t dtype, void* stream) {
+extern "C" int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t C2, int32_t n, int32_t n2,
+                                     int32_t H, int32_t W, int32_t repeat, int32_t Cpad, void* out, int32_t dtype,
+                                     void* stream) {
+  MDX_CHECK_ARG(C2 == 0 || n2 == n || n2 == n * repeat, "mdx_nchw2_to_nhwc_pad: x2 must hold n or n*repeat images");
   MDX_CHECK_ARG(x1 && out && C1 > 0 && C2 >= 0 && (C2 == 0 || x2) && n > 0 && H > 0 && W > 0 && repeat > 0,
                 "mdx_nchw2_to_nhwc_pad: bad arguments");
   MDX_CHECK_ARG(Cpad >= C1 + C2, "mdx_nchw2_to_nhwc_pad: Cpad=%d < C1+C2=%d", Cpad, C1 + C2);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const unsigned g = grid_for((long long)n * repeat * H * W * Cpad);
   if (dtype == MDX_F32)
-    nchw2_to_nhwc_kernel<float><<<g, 256, 0, st>>>(x1, C1, x2, C2, n, H, W, repeat, Cpad, (float*)out);
+    nchw2_to_nhwc_kernel<float><<<g, 256, 0, st>>>(x1, C1, x2, C2, n, n2 > 0 ? n2 : n, H, W, repeat, Cpad, (float*)out);
   else if (dtype == MDX_BF16)
-    nchw2_to_nhwc_kernel<bf16><<<g, 256, 0, st>>>(x1, C1, x2, C2, n, H, W, repeat, Cpad, (bf16*)out);
+    nchw2_to_nhwc_kernel<bf16><<<g, 256, 0, st>>>(x1, C1, x2, C2, n, n2 > 0 ? n2 : n, H, W, repeat, Cpad, (bf16*)out);
   else {
     mdx_set_error("mdx_nchw2_to_nhwc_pad: bad dtype %d", dtype);
     return MDX_ERR_INVALID;

@@ -83,9 +83,13 @@ class LatentDiffusion:
             c_crossattn = c_crossattn[0]
         if isinstance(c_concat, (list, tuple)):
             c_concat = c_concat[0]
-        if c_concat is not None:  # DiffusionWrapper 'concat'/'hybrid' (wukong ddpm.py:364-372)
-            x_noisy = torch.cat((x_noisy, c_concat.to(x_noisy.dtype)), dim=1)
-        return self.unet(x_noisy, t, context=c_crossattn)
+        if c_concat is None:
+            return self.unet(x_noisy, t, context=c_crossattn)
+        self.unet.set_concat(c_concat)  # DiffusionWrapper 'concat'/'hybrid' (wukong ddpm.py:364-372), no torch.cat
+        try:
+            return self.unet(x_noisy, t, context=c_crossattn)
+        finally:
+            self.unet.set_concat(None)
 
     def get_learned_conditioning(self, c):
         if self.cond_stage_model is None:

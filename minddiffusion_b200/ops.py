@@ -485,15 +485,16 @@ def nchw2_to_nhwc(x1, x2, dtype, repeat=1, cpad=None):
     lib = _lib.load()
     x1 = _f32(x1, "x1")
     n, C1, H, W = x1.shape
-    C2 = 0
+    C2, n2 = 0, n
     if x2 is not None:
         x2 = _f32(x2, "x2")
-        if x2.shape[0] != n or x2.shape[2:] != x1.shape[2:]:
-            raise ValueError("x2 must match x1 in batch and size")
+        n2 = x2.shape[0]
+        if n2 not in (n, n * repeat) or x2.shape[2:] != x1.shape[2:]:
+            raise ValueError("x2 must hold n or n*repeat images of x1's size")
         C2 = x2.shape[1]
     cp = cpad or (C1 + C2)
     out = torch.empty((n * repeat, H, W, cp), dtype=dtype, device=x1.device)
-    check(lib.mdx_nchw2_to_nhwc_pad(_p(x1), C1, _p(x2), C2, n, H, W, repeat, cp, _p(out), _DT[dtype], _stream()),
+    check(lib.mdx_nchw2_to_nhwc_pad(_p(x1), C1, _p(x2), C2, n, n2, H, W, repeat, cp, _p(out), _DT[dtype], _stream()),
           "mdx_nchw2_to_nhwc_pad")
     return out
 

@@ -73,8 +73,14 @@ class _GuidedUNet:
         self.unet = model.unet
         self.cfg = not (uncond is None or scale == 1.0)  # plms.py:189
         self.scale = float(scale)
-        if isinstance(cond, dict):
-            raise NotImplementedError("dict conditioning (hybrid / inpaint) is outside this path's scope")
+        c_cat = uc_cat = None
+        if isinstance(cond, dict):  # 'hybrid' conditioning (wukong plms.py:191-201, inpaint.py:92-96)
+            one = lambda v: v[0] if isinstance(v, (list, tuple)) else v
+            c_cat, cond = one(cond.get("c_concat")), one(cond.get("c_crossattn"))
+            if self.cfg:
+                if not isinstance(uncond, dict):
+                    raise AssertionError("unconditional_conditioning must be a dict when conditioning is one")
+                uc_cat, uncond = one(uncond.get("c_concat")), one(uncond.get("c_crossattn"))
         # optional: the two halves of the guided batch on two GPUs (minddiffusion_b200.parallel.CfgPairSplit)
         self.split = getattr(model, "cfg_split", None) if self.cfg else None
         if self.split is not None:
@@ -82,6 +88,12 @@ class _GuidedUNet:
         else:
             ctx = torch.cat((uncond, cond), dim=0) if self.cfg else cond  # order of plms.py:194
         self.unet.set_context(ctx)
+        if c_cat is None:
+            self.unet.set_concat(None)
+        elif self.split is not None:
+            self.unet.set_concat(self.split.my_context(c_cat, uc_cat))
+        else:
+            self.unet.set_concat(torch.cat((uc_cat, c_cat), dim=0) if self.cfg else c_cat)
 
     def __call__(self, x, t_value):
         if self.split is not None:

@@ -62,6 +62,8 @@ def build_parser():
     p.add_argument("--precision", type=str, choices=["full", "autocast"], default="autocast")
     p.add_argument("--enable_lora", default=False, type=lambda s: str(s).lower() in ("1", "true", "yes"))
     p.add_argument("--lora_ckpt_filepath", type=str, default="")
+    p.add_argument("--lora_rank", type=int, default=4, help="unet_config.params.lora_rank of the reference YAML")
+    p.add_argument("--lora_alpha", type=int, default=4, help="unet_config.params.lora_alpha of the reference YAML")
     # additions of this build
     p.add_argument("--ddim", action="store_true", help="use the DDIM sampler (eta-parameterised) instead of PLMS")
     p.add_argument("--token_file", type=str, default="", help=".npy int array [n_prompts, 77] of token ids")
@@ -102,8 +104,12 @@ def load_model(opt, device="cuda"):
         params.update(random_unet_params(unet_cfg, opt.seed))
         params.update(random_decoder_params(dd, opt.seed))
         params.update(random_text_params(text_cfg, opt.seed))
-    if opt.enable_lora:
-        raise NotImplementedError("LoRA deltas (MindPet tk.delta) are merged offline: W += (alpha/r) B A; see SURVEY §8f")
+    if opt.enable_lora:  # txt2img.py:60-63 of wukong-huahua loads the LoRA checkpoint on top of the base one
+        from .weights import merge_lora
+        lora_npz = os.path.splitext(opt.lora_ckpt_filepath)[0] + ".npz"
+        if not os.path.exists(lora_npz):
+            raise FileNotFoundError("--enable_lora needs %s (tools/ckpt_to_npz.py converts a MindSpore .ckpt)" % lora_npz)
+        params = merge_lora(params, dict(np.load(lora_npz)), opt.lora_rank, opt.lora_alpha)
     dtype = torch.float32 if opt.precision == "full" else torch.bfloat16
     unet = UNetModel(params, dtype=dtype, device=device, **unet_cfg)
     unet.use_cuda_graph = True

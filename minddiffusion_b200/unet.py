@@ -115,6 +115,7 @@ class UNetModel:
         self.cout_pad = 16 if self.bf16 else self.out_channels     # conv_out likewise
         self.L = {}
         self._ctx = None
+        self._concat = None          # 'concat' / 'hybrid' conditioning: extra input channels (set_concat)
         self._graphs = {}
         self.use_cuda_graph = False
         self.replayed_launches = 0  # kernels launched by graph replays (they bypass the C ABI's own counter)
@@ -364,6 +365,17 @@ class UNetModel:
     # ------------------------------------------------------------------------------------------------
     # public API
     # ------------------------------------------------------------------------------------------------
+    def set_concat(self, c_concat):
+        """Channel-concatenated conditioning of the 'concat' / 'hybrid' DiffusionWrapper (wukong-huahua ddpm.py:363-372;
+        inpainting: mask + masked-image latents, inpaint.py:78-90).  c_concat: [n, Cc, h, w] for the n images of a
+        forward (n = B*repeat, e.g. cat((uc_concat, c_concat))) or [B, Cc, h, w] to share it between the repeats; None
+        clears it.  The UNet's in_channels must equal the latent channels + Cc."""
+        if c_concat is None:
+            self._concat = None
+        else:
+            self._concat = c_concat.to(device=self.device, dtype=torch.float32).contiguous()
+        self._graphs = {}  # captured graphs read the previous buffer
+
     def set_context(self, context):
         """Hoist the cross-attention K/V projections (attention.py:118-121) out of the step loop: the context is
         constant across sampler steps.  context: [n, L, context_dim] (any float dtype, on the device)."""
@@ -409,7 +421,10 @@ class UNetModel:
         emb_all = ops.conv_direct(emb, L["emb_all"][0], bias=L["emb_all"][1], pre_silu=True)  # [n, sum Cout]
         if uniform_t:
             emb_all = emb_all.expand(n, -1)
-        h = ops.nchw_to_nhwc(x_nchw, self.dtype, repeat=repeat, cpad=self.cin_pad)
+        if self._concat is not None:   # DiffusionWrapper 'concat' / 'hybrid' (wukong ddpm.py:363-372): cat((x, c_concat), 1)
+            h = ops.nchw2_to_nhwc(x_nchw, self._concat, self.dtype, repeat=repeat, cpad=self.cin_pad)
+        else:
+            h = ops.nchw_to_nhwc(x_nchw, self.dtype, repeat=repeat, cpad=self.cin_pad)
         hs = []
 
         def run(pre, layer, h, skip):
@@ -462,6 +477,12 @@ class UNetModel:
         t = timesteps.to(device=self.device, dtype=torch.float32).contiguous()
         if t.numel() != n:
             raise ValueError("timesteps must have %d entries" % n)
+        cc = 0 if self._concat is None else self._concat.shape[1]
+        if x_nchw.shape[1] + cc != self.in_channels:
+            raise ValueError("input has %d (+%d concat) channels, the UNet takes %d" % (x_nchw.shape[1], cc, self.in_channels))
+        if self._concat is not None and (self._concat.shape[0] not in (x_nchw.shape[0], n)
+                                         or self._concat.shape[2:] != x_nchw.shape[2:]):
+            raise ValueError("c_concat must be [B or B*repeat, Cc, h, w] matching the input")
         if not self.use_cuda_graph or taps is not None:
             return self._forward_impl(x_nchw, t, repeat, taps, uniform_t)
         key = (tuple(x_nchw.shape), repeat, uniform_t)

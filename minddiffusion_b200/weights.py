@@ -107,3 +107,38 @@ def random_unet_params(cfg, seed=0, prefix=PREFIX):
             v = gain * rng.standard_normal(shape) / np.sqrt(fan_in)
         P[name] = v.astype(np.float32)
     return P
+
+
+def merge_lora(params, lora_params, lora_rank=4, lora_alpha=4):
+    """Fold LoRA deltas into the dense weights: W' = W + (alpha / rank) * B A.
+
+    The reference swaps `nn.Dense` for MindPet's `tk.delta.LoRADense` in CrossAttention when `enable_lora` is set
+    (wukong-huahua ldm/modules/attention.py:109-127, configs/v1-inference-chinese-lora.yaml:38-40; MindPet is a
+    third-party dependency that is not vendored and not version-pinned by the reference).  MindPet's published
+    forward is  y = x W^T + b + (alpha / rank) * (x A^T) B^T  with `mindpet_delta_lora_a` = A [rank, in] and
+    `mindpet_delta_lora_b` = B [out, rank]; at inference (no dropout) that is a plain dense layer with W' above,
+    so the hot path needs no LoRA kernel.  `lora_params` holds the `*.mindpet_delta_lora_a/_b` arrays (the LoRA
+    checkpoint of txt2img.py --lora_ckpt_filepath); returns a new dict, `params` is not modified."""
+    out = dict(params)
+    scale = float(lora_alpha) / float(lora_rank)
+    merged = 0
+    for key, a in lora_params.items():
+        if not key.endswith("mindpet_delta_lora_a"):
+            continue
+        stem = key[: -len("mindpet_delta_lora_a")]
+        b = lora_params.get(stem + "mindpet_delta_lora_b")
+        wkey = stem + "weight"
+        if b is None or wkey not in out:
+            raise KeyError("LoRA pair for %s is incomplete (need %smindpet_delta_lora_b and %s)" % (key, stem, wkey))
+        a, b = np.asarray(a, dtype=np.float32), np.asarray(b, dtype=np.float32)
+        if a.shape[0] != lora_rank or b.shape[1] != lora_rank:
+            raise ValueError("%s: rank %d/%d does not match lora_rank %d" % (stem, a.shape[0], b.shape[1], lora_rank))
+        w = np.asarray(out[wkey], dtype=np.float32)
+        delta = scale * (b @ a)
+        if delta.shape != w.reshape(w.shape[0], -1).shape:
+            raise ValueError("%s: delta %s does not fit weight %s" % (stem, delta.shape, w.shape))
+        out[wkey] = (w.reshape(delta.shape) + delta).reshape(w.shape)
+        merged += 1
+    if merged == 0:
+        raise ValueError("no *.mindpet_delta_lora_a entries found in lora_params")
+    return out

@@ -170,3 +170,45 @@ def test_oracle_unet_is_deterministic_and_uses_every_parameter():
         Q[name] = P[name] + 0.5
         changed += int(not torch.equal(sd_unet.unet_forward(Q, TINY_UNET_V1, x, t, ctx), y0))
     assert changed == len(names)
+
+
+def test_lora_merge_equals_the_lora_forward():
+    """W' = W + (alpha/rank) B A reproduces MindPet LoRADense's inference forward (weights.merge_lora)."""
+    from minddiffusion_b200.weights import merge_lora
+    rs = np.random.RandomState(0)
+    stem = "model.diffusion_model.input_blocks.1.1.transformer_blocks.0.attn1.to_q."
+    W, A, B = rs.randn(64, 48).astype(np.float32), rs.randn(4, 48).astype(np.float32), rs.randn(64, 4).astype(np.float32)
+    x = rs.randn(5, 48).astype(np.float32)
+    merged = merge_lora({stem + "weight": W, "other": W}, {stem + "mindpet_delta_lora_a": A, stem + "mindpet_delta_lora_b": B},
+                        lora_rank=4, lora_alpha=8)
+    want = x @ W.T + (8 / 4) * (x @ A.T) @ B.T
+    np.testing.assert_allclose(x @ merged[stem + "weight"].T, want, rtol=1e-5, atol=1e-5)
+    assert merged["other"] is W
+    with pytest.raises(ValueError):
+        merge_lora({stem + "weight": W}, {"unrelated": A})
+    with pytest.raises(KeyError):
+        merge_lora({stem + "weight": W}, {stem + "mindpet_delta_lora_a": A})
+
+
+def test_mindspore_checkpoint_converter_round_trip():
+    """tools/ckpt_to_npz.py: parser against a writer of the same checkpoint.proto schema (incl. sliced tensors,
+    negative / large dims encoding, fp16 and bf16 payloads)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ckpt_to_npz", os.path.join(ROOT, "tools", "ckpt_to_npz.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    rs = np.random.RandomState(1)
+    params = {"model.diffusion_model.time_embed.0.weight": rs.randn(7, 300).astype(np.float32),
+              "first_stage_model.decoder.conv_in.bias": rs.randn(5).astype(np.float16),
+              "step": np.array([12345678901], dtype=np.int64), "scalar": np.array(3.5, dtype=np.float32)}
+    for slice_bytes in (None, 1000):
+        got = mod.parse_checkpoint(mod.write_checkpoint(params, slice_bytes))
+        assert list(got) == list(params)
+        for k, v in params.items():
+            assert got[k].dtype == v.dtype and got[k].shape == v.shape and np.array_equal(got[k], v)
+    # bf16 payload: upper halves of fp32 words
+    f = np.array([1.0, -2.5, 0.15625], dtype=np.float32)
+    tensor = b"".join(mod._enc_varint(8) + mod._enc_varint(d) for d in (3,)) + mod._ld(2, b"BFloat16") + mod._ld(
+        3, (f.view(np.uint32) >> 16).astype(np.uint16).tobytes())
+    got = mod.parse_checkpoint(mod._ld(1, mod._ld(1, b"w") + mod._ld(2, tensor)))
+    assert np.array_equal(got["w"], f)

@@ -236,3 +236,41 @@ def test_cuda_path_against_executed_reference_goldens(family, cfg):
             if dtype == torch.float32:
                 assert rel_err(got, ref) < 2e-3, key
         del model
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)], ids=["fp32", "bf16"])
+def test_hybrid_conditioning_inpainting_shape(dtype, tol):
+    """wukong-huahua inpainting (`inpaint.py:78-107`): conditioning is a dict {c_concat: mask + masked-image latents
+    (5 channels), c_crossattn: text}; DiffusionWrapper 'hybrid' concatenates x and c_concat on channels
+    (ddpm.py:369-372) into a 9-channel conv_in.  One guided PLMS run through the sampler API against the oracle's
+    sampler driven by the oracle UNet on the concatenated input."""
+    from minddiffusion_b200 import samplers
+    from oracle import samplers as osamp
+    from oracle import sd_unet
+    cfg = dict(TINY_UNET_V1, in_channels=9)
+    model, Pt = build(cfg, dtype)
+    rs = np.random.RandomState(5)
+    B, hw = 2, 16
+    x_T = torch.from_numpy(rs.randn(B, 4, hw, hw).astype(np.float32))
+    c_cat = torch.from_numpy(rs.randn(B, 5, hw, hw).astype(np.float32))
+    c = torch.from_numpy(rs.randn(B, 77, cfg["context_dim"]).astype(np.float32))
+    uc = torch.from_numpy(rs.randn(B, 77, cfg["context_dim"]).astype(np.float32))
+    ldm = _ldm(model, conditioning_key="hybrid")
+    cond = {"c_concat": c_cat.cuda(), "c_crossattn": c.cuda()}
+    uncond = {"c_concat": [c_cat.cuda()], "c_crossattn": [uc.cuda()]}     # the list form of SD's inpainting script
+    out, _ = samplers.PLMSSampler(ldm).sample(4, B, (4, hw, hw), cond, x_T=x_T.cuda(), verbose=False,
+                                              unconditional_guidance_scale=5.0, unconditional_conditioning=uncond,
+                                              eta=0.0)
+    # oracle: same sampler arithmetic, model = UNet(cat(x, c_concat), t, context)
+    fn = lambda xx, t, cc: sd_unet.unet_forward(Pt, cfg, torch.cat((xx, c_cat.repeat(xx.shape[0] // B, 1, 1, 1)), 1),
+                                                t.to(torch.float32), cc)
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    ref = osamp.plms_sample(fn, sched, 4, x_T, c, uc, 5.0)[0]
+    assert rel_err(out, ref) < tol * 5 and cosine(out, ref) >= 0.999
+    # apply_model with keyword conditioning (wukong ddpm.py:276-278) takes the same route
+    t = torch.full((B,), 500.0)
+    e = ldm.apply_model(x_T.cuda(), t.cuda(), c_concat=c_cat.cuda(), c_crossattn=c.cuda())
+    assert rel_err(e, fn(x_T, t, c)) < tol
+    with pytest.raises(ValueError):
+        model.set_concat(None)
+        model(x_T.cuda(), t.cuda(), context=c.cuda())                     # 4 channels into a 9-channel UNet
