@@ -71,7 +71,8 @@ typedef struct mdx_gemm_args {
   int32_t geglu;
   int32_t block_n;
   int32_t act; /* applied after bias/rowbias, before the residual: 0 none, 1 GELU (tanh form, nn.GELU() of
-                  encoders/text_encoder.py:67-69), 2 QuickGELU x*sigmoid(1.702x) (wukong text_encoder.py:67-74) */
+                  encoders/text_encoder.py:67-69), 2 QuickGELU x*sigmoid(1.702x) (wukong text_encoder.py:67-74),
+                  3 tanh (SRGAN output layer, Taichu-GLIDE model/srgan.py:103) */
   int32_t up_phase; /* 0 = off.  1..4: this launch computes phase (py, px) = ((up_phase-1) >> 1, (up_phase-1) & 1) of
                   Upsample = nearest x2 followed by conv3x3 (openaimodel.py:53-63) WITHOUT materialising the
                   upsampled image: output pixel (2y+py, 2x+px) only sees the 2x2 source window at offset
@@ -317,6 +318,16 @@ int mdx_nchw2_to_nhwc_pad(const float* x1, int32_t C1, const float* x2, int32_t 
 int mdx_sampler_glide_step(const void* model_out, int64_t ld_out, int32_t model_dtype, int32_t cfg, float scale,
                            int32_t mode, const float* x, const float* coef_host, const float* noise, float* x_prev,
                            float* pred_xstart, int32_t P, int32_t C, int32_t h, int32_t w, void* stream);
+
+/* SRGAN x4 stage of the GLIDE cascade (model/srgan.py).
+ * mdx_prelu — nn.PReLU(C) on NHWC rows: out = prelu(x; slope[c]) (+ residual, added after the activation; slope
+ *      NULL = plain add: `conv1 + conv2` of Generator.construct, srgan.py:100, and ResidualBlock's `out + x`, :54).
+ * mdx_depth_to_space2 — ops.DepthToSpace(2) (srgan.py:62) on NHWC fused with the PReLU that follows it:
+ *      out[n, 2h+i, 2w+j, c] = prelu(x[n, h, w, (2i+j)*C + c]); x has 4C channels, slope may be NULL. */
+int mdx_prelu(const void* x, int64_t ldx, int64_t rows, int32_t C, const float* slope, const void* residual,
+              int64_t ldr, void* out, int64_t ldo, int32_t in_dtype, int32_t out_dtype, void* stream);
+int mdx_depth_to_space2(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, const float* slope, void* out,
+                        int32_t in_dtype, int32_t out_dtype, void* stream);
 
 #ifdef __cplusplus
 }

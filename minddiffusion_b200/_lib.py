@@ -101,6 +101,8 @@ SIGNATURES = {
     "mdx_resize_bilinear": (c_int, [c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_p]),
     "mdx_nchw2_to_nhwc_pad": (c_int, [c_p, c_int, c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_p, c_int,
                                       c_p]),
+    "mdx_prelu": (c_int, [c_p, c_i64, c_i64, c_int, c_p, c_p, c_i64, c_p, c_i64, c_int, c_int, c_p]),
+    "mdx_depth_to_space2": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p, c_p, c_int, c_int, c_p]),
     "mdx_sampler_glide_step": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_int, c_p, c_p, c_p, c_p, c_p, c_int, c_int,
                                        c_int, c_int, c_p]),
 }

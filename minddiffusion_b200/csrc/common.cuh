@@ -110,15 +110,17 @@ __device__ __forceinline__ void geglu_pair(float& o0, float& o1, float v0, float
   fmul2v(o0, o1, v0, v1, g0, g1);
 }
 
-// epilogue activations: 1 = GELU (tanh form), 2 = QuickGELU x * sigmoid(1.702 x)
+// epilogue activations: 1 = GELU (tanh form), 2 = QuickGELU x * sigmoid(1.702 x), 3 = tanh (SRGAN output, srgan.py:103)
 __device__ __forceinline__ float apply_act(float x, int act) {
   if (act == 1) return gelu_tanh_fast(x);
   if (act == 2) return x / (1.f + __expf(-1.702f * x));
+  if (act == 3) return tanhf(x);
   return x;
 }
 __device__ __forceinline__ float apply_act_precise(float x, int act) {
   if (act == 1) return gelu_tanh_f(x);
   if (act == 2) return x / (1.f + expf(-1.702f * x));
+  if (act == 3) return tanhf(x);
   return x;
 }
 

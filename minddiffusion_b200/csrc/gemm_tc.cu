@@ -690,7 +690,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   if (a->geglu)
     MDX_CHECK_ARG(!a->rowbias && !a->residual && !a->act && a->N % 32 == 0 && a->out_dtype == MDX_BF16,
                   "mdx_gemm_tc: geglu excludes rowbias/residual/act and writes bf16");
-  MDX_CHECK_ARG(a->act >= 0 && a->act <= 2, "mdx_gemm_tc: act must be 0, 1 (gelu) or 2 (quick gelu)");
+  MDX_CHECK_ARG(a->act >= 0 && a->act <= 3, "mdx_gemm_tc: act must be 0, 1 (gelu), 2 (quick gelu) or 3 (tanh)");
   if (a->act) MDX_CHECK_ARG(!a->rowbias, "mdx_gemm_tc: act excludes rowbias");
 
   TcParams p;

@@ -123,6 +123,41 @@ __global__ void nchw2_to_nhwc_kernel(const float* __restrict__ x1, int C1, const
   }
 }
 
+// nn.PReLU(C) on NHWC rows (srgan.py:45,63,80,88): y = x > 0 ? x : slope[c] * x, optional "+ residual" first
+// (the `conv1 + conv2` sum of Generator.construct feeds no PReLU, so residual is added AFTER the activation).
+template <typename TI, typename TO>
+__global__ void prelu_kernel(const TI* __restrict__ x, long long ldx, long long rows, int C, const float* __restrict__ slope,
+                             const TI* __restrict__ residual, long long ldr, TO* __restrict__ out, long long ldo) {
+  const long long total = rows * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long r = i / C;
+    float v = to_f32<TI>(x[r * ldx + c]);
+    if (slope) v = v > 0.f ? v : slope[c] * v;
+    if (residual) v += to_f32<TI>(residual[r * ldr + c]);
+    out[r * ldo + c] = from_f32<TO>(v);
+  }
+}
+
+// ops.DepthToSpace(2) (srgan.py:62) on NHWC, fused with the PReLU that follows it:
+// out[n, 2h+i, 2w+j, c] = prelu(in[n, h, w, (2i+j)*C + c])   (depth index = block offset major, "DCR")
+template <typename TI, typename TO>
+__global__ void depth_to_space2_kernel(const TI* __restrict__ x, int n, int H, int W, int C, const float* __restrict__ slope,
+                                       TO* __restrict__ out) {
+  const long long total = (long long)n * 4 * H * W * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long r = i / C;
+    const int ow = (int)(r % (2 * W)); r /= 2 * W;
+    const int oh = (int)(r % (2 * H));
+    const int b = (int)(r / (2 * H));
+    const int blk = (oh & 1) * 2 + (ow & 1);
+    float v = to_f32<TI>(x[((((long long)b * H + (oh >> 1)) * W + (ow >> 1)) * 4 + blk) * C + c]);
+    if (slope) v = v > 0.f ? v : slope[c] * v;
+    out[i] = from_f32<TO>(v);
+  }
+}
+
 struct GlideP {
   const void* model_out; long long ld;
   int cfg; float scale; int mode;
@@ -296,6 +331,46 @@ extern "C" int mdx_sampler_glide_step(const void* model_out, int64_t ld_out, int
   const long long total = (long long)P * C * h * w;
   if (model_dtype == MDX_BF16) glide_step_kernel<bf16><<<grid_for(total), 256, 0, st>>>(p);
   else glide_step_kernel<float><<<grid_for(total), 256, 0, st>>>(p);
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}
+
+extern "C" int mdx_prelu(const void* x, int64_t ldx, int64_t rows, int32_t C, const float* slope, const void* residual,
+                         int64_t ldr, void* out, int64_t ldo, int32_t in_dtype, int32_t out_dtype, void* stream) {
+  MDX_CHECK_ARG(x && out && rows > 0 && C > 0 && (slope || residual), "mdx_prelu: bad arguments");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const unsigned g = grid_for(rows * C);
+  if (in_dtype == MDX_F32 && out_dtype == MDX_F32)
+    prelu_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, ldx, rows, C, slope, (const float*)residual, ldr, (float*)out, ldo);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_BF16)
+    prelu_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, ldx, rows, C, slope, (const float*)residual, ldr, (bf16*)out, ldo);
+  else if (in_dtype == MDX_BF16 && out_dtype == MDX_BF16)
+    prelu_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, ldx, rows, C, slope, (const bf16*)residual, ldr, (bf16*)out, ldo);
+  else {
+    mdx_set_error("mdx_prelu: unsupported dtypes %d -> %d", in_dtype, out_dtype);
+    return MDX_ERR_INVALID;
+  }
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}
+
+extern "C" int mdx_depth_to_space2(const void* x, int32_t n, int32_t H, int32_t W, int32_t C, const float* slope,
+                                   void* out, int32_t in_dtype, int32_t out_dtype, void* stream) {
+  MDX_CHECK_ARG(x && out && n > 0 && H > 0 && W > 0 && C > 0, "mdx_depth_to_space2: bad arguments");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const unsigned g = grid_for((long long)n * 4 * H * W * C);
+  if (in_dtype == MDX_F32 && out_dtype == MDX_F32)
+    depth_to_space2_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, slope, (float*)out);
+  else if (in_dtype == MDX_F32 && out_dtype == MDX_BF16)
+    depth_to_space2_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, n, H, W, C, slope, (bf16*)out);
+  else if (in_dtype == MDX_BF16 && out_dtype == MDX_BF16)
+    depth_to_space2_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, n, H, W, C, slope, (bf16*)out);
+  else {
+    mdx_set_error("mdx_depth_to_space2: unsupported dtypes %d -> %d", in_dtype, out_dtype);
+    return MDX_ERR_INVALID;
+  }
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;

@@ -64,7 +64,7 @@ def pick_block_n(N, geglu=False):
     return int(_lib.load().mdx_gemm_tc_pick_block_n(N, 1 if geglu else 0))
 
 
-ACT = {None: 0, "gelu": 1, "quick_gelu": 2}
+ACT = {None: 0, "gelu": 1, "quick_gelu": 2, "tanh": 3}
 
 
 def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
@@ -513,3 +513,30 @@ def sampler_glide_step(model_out, x, coef, cfg, scale, mode, noise=None, x_prev=
                                      _p(_f32(noise, "noise")), _p(x_prev), _p(pred_xstart), P, C, h, wd, _stream()),
           "mdx_sampler_glide_step")
     return x_prev
+
+
+def prelu(x, slope=None, residual=None, out_dtype=None):
+    """nn.PReLU(C) over NHWC rows (+ residual added after it); slope None = plain residual add."""
+    lib = _lib.load()
+    rows, C, ldx = _rows_ld(x)
+    out = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
+    ldr = 0
+    if residual is not None:
+        rr, rc, ldr = _rows_ld(residual)
+        if rr != rows or rc != C or residual.dtype != x.dtype:
+            raise ValueError("residual must match x")
+    check(lib.mdx_prelu(_p(x), ldx, rows, C, _p(_f32(slope, "slope")), _p(residual), ldr, _p(out), C, _dt(x), _dt(out),
+                        _stream()), "mdx_prelu")
+    return out
+
+
+def depth_to_space2(x, slope=None, out_dtype=None):
+    """ops.DepthToSpace(2) on NHWC [n, H, W, 4C] -> [n, 2H, 2W, C], fused with a PReLU(C) when slope is given."""
+    lib = _lib.load()
+    n, H, W, C4 = x.shape
+    if not x.is_contiguous() or C4 % 4:
+        raise ValueError("x must be contiguous with a channel count divisible by 4")
+    out = torch.empty((n, 2 * H, 2 * W, C4 // 4), dtype=out_dtype or x.dtype, device=x.device)
+    check(lib.mdx_depth_to_space2(_p(x), n, H, W, C4 // 4, _p(_f32(slope, "slope")), _p(out), _dt(x), _dt(out), _stream()),
+          "mdx_depth_to_space2")
+    return out

@@ -344,3 +344,35 @@ def ddim_loop(P, o, samples, token, mask, x_T, eta=0.0):
         sigma = eta * torch.sqrt((1 - abp) / (1 - ab)) * torch.sqrt((1 - ab) / abp)
         img = torch.sqrt(1 - abp - sigma * sigma) * eps + x0 * torch.sqrt(abp)
     return img
+
+
+# ---------------------------------------------------------------------------------------------------------
+# SRGAN x4 stage (model/srgan.py)
+# ---------------------------------------------------------------------------------------------------------
+def depth_to_space2(x):
+    """ops.DepthToSpace(2) on NCHW: out[n, c, 2h+i, 2w+j] = x[n, (2i+j)*C + c, h, w] (block offset is the major part
+    of the depth index, as MindSpore / TensorFlow document it; NOT torch's pixel_shuffle order)."""
+    n, c4, h, w = x.shape
+    c = c4 // 4
+    return x.reshape(n, 2, 2, c, h, w).permute(0, 3, 4, 1, 5, 2).reshape(n, c, 2 * h, 2 * w)
+
+
+def srgan_forward(P, x, upscale_factor=4):
+    """Generator.construct (srgan.py:96-104) with ResidualBlock (:47-54) and SubpixelConvolutionLayer (:64-68);
+    nn.BatchNorm2d in inference mode (moving statistics, eps 1e-5), nn.PReLU(C) with per-channel slopes `w`."""
+    P = {k: (v if isinstance(v, torch.Tensor) else torch.from_numpy(np.asarray(v))).float() for k, v in P.items()}
+    conv2d = lambda p, t, pad: F.conv2d(t, P[p + "weight"], P[p + "bias"], padding=pad)
+    bn = lambda p, t: F.batch_norm(t, P[p + "moving_mean"], P[p + "moving_variance"], P[p + "gamma"], P[p + "beta"],
+                                   False, 0.0, 1e-5)
+    prelu = lambda p, t: F.prelu(t, P[p + "w"])
+    c1 = prelu("conv1.1.", conv2d("conv1.0.", x.float(), 4))
+    t = c1
+    for i in range(16):
+        p = "trunk.%d." % i
+        u = prelu(p + "prelu.", bn(p + "bn1.", conv2d(p + "conv1.", t, 1)))
+        t = bn(p + "bn2.", conv2d(p + "conv2.", u, 1)) + t
+    out = c1 + prelu("conv2.1.", conv2d("conv2.0.", t, 1))
+    for i in range(int(math.log(upscale_factor, 2))):
+        p = "subpixel_conv.%d." % i
+        out = prelu(p + "prelu.", depth_to_space2(conv2d(p + "conv.", out, 1)))
+    return torch.tanh(conv2d("conv3.", out, 4))

@@ -223,6 +223,35 @@ class _Linear(Cell):
         return _wrap(F.linear(x.to(dt), self.weight.to(dt), self.bias.to(dt)))
 
 
+class BatchNorm2d(Cell):
+    """Inference mode: moving statistics (the reference never puts the SRGAN generator in training mode)."""
+
+    def __init__(self, num_features, eps=1e-5, momentum=0.9, affine=True, gamma_init="ones", beta_init="zeros",
+                 moving_mean_init="zeros", moving_var_init="ones", use_batch_statistics=None, data_format="NCHW"):
+        super().__init__()
+        self.eps = eps
+        self.gamma, self.beta = Parameter(torch.ones(num_features)), Parameter(torch.zeros(num_features))
+        self.moving_mean = Parameter(torch.zeros(num_features), requires_grad=False)
+        self.moving_variance = Parameter(torch.ones(num_features), requires_grad=False)
+
+    def construct(self, x):
+        return _wrap(F.batch_norm(x, self.moving_mean, self.moving_variance, self.gamma, self.beta, False, 0.0, self.eps))
+
+
+class PReLU(Cell):
+    def __init__(self, channel=1, w=0.25):
+        super().__init__()
+        self.w = Parameter(torch.full((channel,), float(w)))
+
+    def construct(self, x):
+        return _wrap(F.prelu(x, self.w))
+
+
+class Tanh(Cell):
+    def construct(self, x):
+        return _wrap(torch.tanh(x))
+
+
 class _Unused(Cell):
     def __init__(self, *a, **k):
         super().__init__()
@@ -316,7 +345,8 @@ class Softmax(Cell):
 
 for _n, _c in dict(Cell=Cell, Dense=Dense, Conv2d=Conv2d, Conv1d=Conv1d, Conv3d=_Unused, AvgPool1d=_Unused,
                    AvgPool2d=AvgPool2d, Embedding=Embedding, GroupNorm=GroupNorm, LayerNorm=LayerNorm, SiLU=SiLU, GELU=GELU,
-                   Dropout=Dropout, SequentialCell=SequentialCell, Sequential=SequentialCell, CellList=CellList,
+                   Dropout=Dropout, BatchNorm2d=BatchNorm2d, PReLU=PReLU, Tanh=Tanh, Conv2dTranspose=_Unused,
+                   SequentialCell=SequentialCell, Sequential=SequentialCell, CellList=CellList,
                    MSELoss=MSELoss, Softmax=Softmax, Sigmoid=Sigmoid, Pad=_Unused).items():
     setattr(nn, _n, _c)
 
@@ -406,6 +436,9 @@ _prims = dict(
     Round=lambda s, x: torch.round(x), Sin=lambda s, x: torch.sin(x), Print=lambda s, *a: None,
     UniformReal=lambda s, shape: torch.rand(_shape(shape)),
     ResizeBilinear=lambda s, x: _resize_bilinear_legacy(x, s.a[0]),
+    DepthToSpace=lambda s, x: x.reshape(x.shape[0], s.a[0], s.a[0], x.shape[1] // (s.a[0] ** 2), x.shape[2],
+                                        x.shape[3]).permute(0, 3, 4, 1, 5, 2).reshape(
+        x.shape[0], x.shape[1] // (s.a[0] ** 2), x.shape[2] * s.a[0], x.shape[3] * s.a[0]),
     Zeros=lambda s, shape, dtype=float32: torch.zeros(_shape(shape), dtype=dtype),
     ZerosLike=lambda s, x: torch.zeros_like(x),
     Transpose=lambda s, x, perm: x.permute(*perm),
@@ -501,9 +534,25 @@ class TruncatedNormal:
 initializer_mod.TruncatedNormal = TruncatedNormal
 
 
+class Normal:
+    def __init__(self, sigma=0.01, mean=0.0):
+        self.sigma, self.mean = sigma, mean
+
+
+class XavierUniform:
+    def __init__(self, gain=1):
+        self.gain = gain
+
+
+initializer_mod.Normal = Normal
+initializer_mod.XavierUniform = XavierUniform
+
+
 def initializer(init, shape=None, dtype=float32):
     if isinstance(init, TruncatedNormal):  # values are overwritten by the seeded weights anyway
         return Tensor(torch.randn(_shape(shape)).clamp_(-2, 2) * init.sigma, dtype)
+    if isinstance(init, Normal):
+        return Tensor(torch.randn(_shape(shape)) * init.sigma + init.mean, dtype)
     if init == "zeros":
         return Tensor(torch.zeros(_shape(shape), dtype=dtype))
     if init == "ones":

@@ -279,3 +279,54 @@ def test_cuda_glide_shipped_architectures_bf16():
             out = glide.create_upsample_model(P, **opts)(x.cuda(), t.cuda(), lr.cuda(), tok.cuda(), mask.cuda())
         assert tuple(out.shape) == tuple(ref.shape)
         assert rel(out, ref) < 2e-2, (size, rel(out, ref))
+
+
+# ------------------------------------------------------------------------------------------------------------
+# SRGAN x4 stage
+# ------------------------------------------------------------------------------------------------------------
+def srgan_golden():
+    return dict(np.load(os.path.join(ROOT, "tests", "golden", "srgan_golden.npz")))
+
+
+def test_oracle_srgan_matches_executed_reference():
+    from minddiffusion_b200.srgan import random_srgan_params, srgan_param_shapes
+    from oracle import glide as og
+    G = srgan_golden()
+    y = og.srgan_forward(random_srgan_params(4, 0), T_(G["x"]))
+    assert tuple(y.shape) == (2, 3, 48, 32) and rel(y, G["y"]) < 1e-6
+    n = sum(int(np.prod(s)) for k, s in srgan_param_shapes(4).items() if "moving" not in k)
+    assert 1.5e6 < n < 1.6e6                                   # SRGAN generator: ~1.55 M parameters
+    # DepthToSpace convention: the block offset is the major part of the depth index
+    x = torch.arange(2 * 8 * 1 * 1).reshape(2, 8, 1, 1).float()
+    d = og.depth_to_space2(x)
+    assert d.shape == (2, 2, 2, 2) and d[0, 0].flatten().tolist() == [0.0, 2.0, 4.0, 6.0] and d[0, 1, 0, 0] == 1.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)], ids=["fp32", "bf16"])
+def test_cuda_srgan_against_golden(dtype, tol):
+    from minddiffusion_b200.srgan import SRGAN, random_srgan_params
+    G = srgan_golden()
+    net = SRGAN(4, random_srgan_params(4, 0), dtype=dtype)
+    y = net.sr_handle(T_(G["x"]).cuda())
+    assert tuple(y.shape) == (2, 3, 48, 32) and y.dtype == torch.float32
+    assert rel(y, G["y"]) < tol
+    assert float(y.abs().max()) <= 1.0
+
+
+@pytest.mark.gpu
+def test_srgan_kernels_against_torch():
+    import torch.nn.functional as F
+    from minddiffusion_b200 import ops
+    from oracle import glide as og
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 5, 6, 64, generator=g)
+    slope, res = torch.rand(64, generator=g), torch.randn(2, 5, 6, 64, generator=g)
+    ref = F.prelu(x.permute(0, 3, 1, 2), slope).permute(0, 2, 3, 1)
+    assert torch.equal(ops.prelu(x.cuda(), slope.cuda()).cpu(), ref)
+    assert torch.allclose(ops.prelu(x.cuda(), slope.cuda(), residual=res.cuda()).cpu(), ref + res, atol=1e-6)
+    assert torch.allclose(ops.prelu(x.cuda(), None, residual=res.cuda()).cpu(), x + res, atol=1e-6)
+    y = torch.randn(2, 3, 4, 32, generator=g)
+    ref = F.prelu(og.depth_to_space2(y.permute(0, 3, 1, 2)), slope[:8]).permute(0, 2, 3, 1)
+    assert torch.equal(ops.depth_to_space2(y.cuda(), slope[:8].cuda()).cpu(), ref)
+    assert torch.equal(ops.depth_to_space2(y.cuda()).cpu(), og.depth_to_space2(y.permute(0, 3, 1, 2)).permute(0, 2, 3, 1))
