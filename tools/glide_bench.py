@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--scale", type=float, default=5.0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--skip-up", action="store_true")
+    ap.add_argument("--srgan", action="store_true", help="also run the SRGAN x4 stage (256 -> 1024) on the result")
     a = ap.parse_args()
     P = a.batch
     ob = glide.model_and_diffusion_defaults(timestep_respacing=a.base_steps)
@@ -61,6 +62,13 @@ def main():
         up = timed(lambda: glide.ddim_sample_loop(sm, (P, 3, 256, 256), samples, tok2, mask[:P], sm.num_timesteps),
                    "upsampler", sm.num_timesteps)
         assert torch.isfinite(up).all()
+        if a.srgan:
+            from minddiffusion_b200.srgan import SRGAN
+            sr = SRGAN(4)
+            chunk = 8                                   # 1024^2 x 64-channel fp32 activations: 268 MB per image
+            big = timed(lambda: torch.cat([sr.sr_handle(up[i:i + chunk].clamp(-1, 1)) for i in range(0, P, chunk)]),
+                        "srgan", 1)
+            assert tuple(big.shape) == (P, 3, 1024, 1024) and torch.isfinite(big).all()
     total = sum(v["ms"] for v in res.values())
     print(json.dumps({"workload": "Taichu-GLIDE cascade, batch %d" % P, "images_per_sec": P / (total / 1e3),
                       "total_ms": total, **res}))
