@@ -178,9 +178,10 @@ int mdx_layernorm(const void* x, int64_t ldx, int32_t rows, int32_t C, float eps
  * (CrossAttention.construct, attention.py:117-166; heads are interleaved in the channel dim, so the
  * rearange_in/out transposes at attention.py:124-133,154-163 become strides).
  *  q: [batch, Nq, heads*d] (row stride ldq), k/v: [batch, Nk, heads*d] (ldk/ldv), o: [batch, Nq, heads*d] (ldo).
- *  Batch strides are Nq*ldq etc. (tensors are dense over batch).  dtype MDX_BF16, d == 64, not causal: the
+ *  Batch strides are Nq*ldq etc. (tensors are dense over batch).  dtype MDX_BF16, d <= 64, not causal: the
  *  tcgen05 kernels of attention_tc.cu (S / P / O in tensor memory, TMA-fed; a two-CTA-per-SM single-tile variant
- *  when Nk <= 128); other head dims: flash kernel on mma.sync tensor cores; both with fp32 softmax.
+ *  when Nk <= 128; d < 64 is zero-padded to 64 by the TMA box); larger head dims and causal: flash kernel on
+ *  mma.sync tensor cores; all with fp32 softmax.
  *  MDX_F32: CUDA-core check-mode kernel.  d <= 160, d % 8 == 0.
  *  causal != 0: key j is visible to query i only if j <= i (the text tower's triu(-inf, 1) mask,
  *  encoders/text_encoder.py:131-134); uses the mma.sync kernel for every head dim.

@@ -283,7 +283,8 @@ int launch_fa(const AttnP& p, cudaStream_t st) {
 }  // namespace
 
 int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                         void* o, long long ldo, int batch, int heads, int Nq, int Nk, float scale, cudaStream_t st);
+                         void* o, long long ldo, int batch, int heads, int Nq, int Nk, int d, float scale,
+                         cudaStream_t st);
 
 extern "C" int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                              void* o, int64_t ldo, int32_t batch, int32_t heads, int32_t Nq, int32_t Nk, int32_t d,
@@ -305,10 +306,11 @@ extern "C" int mdx_attention(const void* q, int64_t ldq, const void* k, int64_t 
   MDX_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 2 == 0, "mdx_attention: row strides must be multiples of 8");
   MDX_CHECK_ARG(((uintptr_t)q & 15) == 0 && ((uintptr_t)k & 15) == 0 && ((uintptr_t)v & 15) == 0 && ((uintptr_t)o & 3) == 0,
                 "mdx_attention: operands must be 16-byte aligned");
-  // head dim 64 (every attention layer of the SD2 UNet): tcgen05/TMEM kernel; MDX_ATTN_LEGACY=1 keeps mma.sync
-  static const bool legacy = getenv("MDX_ATTN_LEGACY") != nullptr;
-  if (d == 64 && !legacy && !causal && ldo % 8 == 0 && ((uintptr_t)o & 15) == 0)
-    return mdx_attention_tc_d64(q, ldq, k, ldk, v, ldv, o, ldo, batch, heads, Nq, Nk, scale, st);
+  // head dim <= 64 (every attention layer of the SD2 UNet is 64; wukong-huahua's 64x64 level is 40, zero-padded to
+  // 64 by TMA): tcgen05/TMEM kernels; MDX_ATTN_LEGACY=1 keeps mma.sync
+  const bool legacy = getenv("MDX_ATTN_LEGACY") != nullptr;
+  if (d <= 64 && !legacy && !causal && ldo % 8 == 0 && ((uintptr_t)o & 15) == 0)
+    return mdx_attention_tc_d64(q, ldq, k, ldk, v, ldv, o, ldo, batch, heads, Nq, Nk, d, scale, st);
   if (d <= 48) return launch_fa<48>(p, st);
   if (d <= 64) return launch_fa<64>(p, st);
   if (d <= 80) return launch_fa<80>(p, st);

@@ -35,6 +35,7 @@ struct AttnTcP {
   float sl2;  // scale * log2(e)
   bf16* o;
   long long ldo;
+  int d;  // head dim <= 64; the operand tiles are zero-padded to 64 columns by TMA
 };
 
 // smem map (offsets from the 1024-aligned base)
@@ -155,15 +156,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (elect_one()) {
       // ===================== TMA producer =====================
       mbar_arrive_expect_tx(q_full, TILE_BYTES);
-      tma_load_3d(smem + OFF_Q, &tmQ, q_full, head * AT_D, q0, b);
+      tma_load_4d(smem + OFF_Q, &tmQ, q_full, 0, head, q0, b);
       for (int j = 0; j < T; ++j) {
         const int ks = j % AT_KS, vs = j % AT_VS;
         mbar_wait(&k_empty[ks], ((j / AT_KS) & 1) ^ 1);
         mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
-        tma_load_3d(smem + OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], head * AT_D, j * AT_BN, b);
+        tma_load_4d(smem + OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], 0, head, j * AT_BN, b);
         mbar_wait(&v_empty[vs], ((j / AT_VS) & 1) ^ 1);
         mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
-        tma_load_3d(smem + OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], head * AT_D, j * AT_BN, b);
+        tma_load_4d(smem + OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
       }
     }
   } else if (warp == 1) {
@@ -343,9 +344,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       const float w1 = (m1 == -INFINITY) ? 0.f : ex2_approx((m1 - m) * c);
       const float inv = 1.f / (l_run * w0 + l1 * w1);
       if (q0 + row < p.Nq) {
-        bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * AT_D;
+        bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * p.d;
 #pragma unroll
         for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+        if (v8 * 8 >= p.d) break;
           float f[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) f[i] = (o_acc[v8 * 8 + i] * w0 + xch[(v8 * 8 + i) * AT_BM + row] * w1) * inv;
@@ -421,10 +423,10 @@ attn_tc_single_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     if (warp == 0) {
       if (elect_one()) {
         mbar_arrive_expect_tx(qk_full, 2 * TILE_BYTES);
-        tma_load_3d(smem, &tmQ, qk_full, head * AT_D, q0, b);
-        tma_load_3d(smem + TILE_BYTES, &tmK, qk_full, head * AT_D, 0, b);
+        tma_load_4d(smem, &tmQ, qk_full, 0, head, q0, b);
+        tma_load_4d(smem + TILE_BYTES, &tmK, qk_full, 0, head, 0, b);
         mbar_arrive_expect_tx(v_full, TILE_BYTES);
-        tma_load_3d(smem + 2 * TILE_BYTES, &tmV, v_full, head * AT_D, 0, b);
+        tma_load_4d(smem + 2 * TILE_BYTES, &tmV, v_full, 0, head, 0, b);
       }
     } else if (warp == 1) {
       if (elect_one()) {
@@ -497,9 +499,10 @@ attn_tc_single_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tmem_ld_wait();
     tc_fence_before();
     if (q0 + row < p.Nq) {
-      bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * AT_D;
+      bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * p.d;
 #pragma unroll
       for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+        if (v8 * 8 >= p.d) break;
         uint4 u;
         u.x = pack_bf16x2(__uint_as_float(r[v8 * 8]) * inv, __uint_as_float(r[v8 * 8 + 1]) * inv);
         u.y = pack_bf16x2(__uint_as_float(r[v8 * 8 + 2]) * inv, __uint_as_float(r[v8 * 8 + 3]) * inv);
@@ -535,18 +538,20 @@ EncodeTiledFn at_encode_fn() {
   return fn;
 }
 
-// [batch, rows, heads*64] bf16 view with row stride ld: box = 64 channels x 128 rows x 1 batch
-int make_map_qkv(CUtensorMap* m, const void* ptr, long long ld, int width, int rows, int batch) {
+// [batch, rows, heads, d] bf16 view (row stride ld, heads packed d apart): box = 64 channels x 1 head x 128 rows x 1
+// batch.  For d < 64 the box runs past the head's d channels; TMA zero-fills those columns, which adds nothing to
+// q k^T and leaves the padded output columns (never stored) at zero.
+int make_map_qkv(CUtensorMap* m, const void* ptr, long long ld, int d, int heads, int rows, int batch) {
   EncodeTiledFn enc = at_encode_fn();
   if (!enc) {
     mdx_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
     return MDX_ERR_CUDA;
   }
-  cuuint64_t dims[3] = {(cuuint64_t)width, (cuuint64_t)rows, (cuuint64_t)batch};
-  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows * ld * 2};
-  cuuint32_t box[3] = {64, 128, 1};
-  cuuint32_t es[3] = {1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, es,
+  cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)heads, (cuuint64_t)rows, (cuuint64_t)batch};
+  cuuint64_t strides[3] = {(cuuint64_t)d * 2, (cuuint64_t)ld * 2, (cuuint64_t)rows * ld * 2};
+  cuuint32_t box[4] = {64, 1, 128, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -558,15 +563,15 @@ int make_map_qkv(CUtensorMap* m, const void* ptr, long long ld, int width, int r
 
 }  // namespace
 
-// Internal entry (called by mdx_attention for bf16, d == 64).
+// Internal entry (called by mdx_attention for bf16, d <= 64, d % 8 == 0, not causal).
 int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                         void* o, long long ldo, int batch, int heads, int Nq, int Nk, float scale,
+                         void* o, long long ldo, int batch, int heads, int Nq, int Nk, int d, float scale,
                          cudaStream_t st) {
   CUtensorMap mq, mk, mv;
   int rc;
-  if ((rc = make_map_qkv(&mq, q, ldq, heads * AT_D, Nq, batch))) return rc;
-  if ((rc = make_map_qkv(&mk, k, ldk, heads * AT_D, Nk, batch))) return rc;
-  if ((rc = make_map_qkv(&mv, v, ldv, heads * AT_D, Nk, batch))) return rc;
+  if ((rc = make_map_qkv(&mq, q, ldq, d, heads, Nq, batch))) return rc;
+  if ((rc = make_map_qkv(&mk, k, ldk, d, heads, Nk, batch))) return rc;
+  if ((rc = make_map_qkv(&mv, v, ldv, d, heads, Nk, batch))) return rc;
   static bool attr_set = false;
   if (!attr_set) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
@@ -575,7 +580,7 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
   }
   AttnTcP p;
   p.Nq = Nq; p.Nk = Nk; p.sl2 = scale * 1.4426950408889634f;
-  p.o = reinterpret_cast<bf16*>(o); p.ldo = ldo;
+  p.o = reinterpret_cast<bf16*>(o); p.ldo = ldo; p.d = d;
   dim3 grid((Nq + AT_BM - 1) / AT_BM, heads, batch);
   if (Nk <= AT_BN && !getenv("MDX_ATTN_NO_SINGLE"))
     attn_tc_single_kernel<<<grid, 256, AT1_SMEM, st>>>(mq, mk, mv, p);

@@ -371,10 +371,16 @@ class UNetModel:
         forward (n = B*repeat, e.g. cat((uc_concat, c_concat))) or [B, Cc, h, w] to share it between the repeats; None
         clears it.  The UNet's in_channels must equal the latent channels + Cc."""
         if c_concat is None:
-            self._concat = None
+            if self._concat is not None:
+                self._concat = None
+                self._graphs = {}  # captured graphs read the previous buffer
+            return
+        c = c_concat.to(device=self.device, dtype=torch.float32)
+        if self._concat is not None and self._concat.shape == c.shape:
+            self._concat.copy_(c)  # same shape: refill the buffer the captured graphs read
         else:
-            self._concat = c_concat.to(device=self.device, dtype=torch.float32).contiguous()
-        self._graphs = {}  # captured graphs read the previous buffer
+            self._concat = c.contiguous().clone()
+            self._graphs = {}
 
     def set_context(self, context):
         """Hoist the cross-attention K/V projections (attention.py:118-121) out of the step loop: the context is
