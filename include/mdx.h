@@ -48,7 +48,7 @@ int64_t mdx_launch_count(void);
  *     ; geglu (optional): N is 2*I laid out per BLOCK_N tile as [value half | gate half] (see pack_geglu in
  *     minddiffusion_b200/weights.py), out[p, j] = value * gelu_tanh(gate), out has I columns
  *     ; + residual[p * ldr + n] (bf16 or fp32, optional) ; store bf16 (out_dtype MDX_BF16) or fp32 (MDX_F32).
- *  block_n: 0 = choose automatically; otherwise one of 64, 128, 160, 256 (geglu packing must match).
+ *  block_n: 0 = choose automatically; otherwise one of 64, 128, 160, 192, 256 (geglu packing must match).
  * --------------------------------------------------------------------------------------------------------- */
 typedef struct mdx_gemm_args {
   int32_t nseg;

@@ -57,7 +57,7 @@ struct TcParams {
 
 template <int BN> struct TcCfg {
   static constexpr int B_STAGE_BYTES = BN * BK * 2;
-  static constexpr int STAGES = (BN >= 256) ? 3 : (BN >= 128 ? 5 : 7);
+  static constexpr int STAGES = (BN >= 256) ? 3 : (BN >= 192 ? 4 : (BN >= 128 ? 5 : 7));
   static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
   static constexpr int EPI_WARPS = 12;                        // 4 TMEM lane quadrants x 3 column shares
   static constexpr int THREADS = 128 + 32 * EPI_WARPS;        // 512: one role warpgroup + three epilogue warpgroups
@@ -645,6 +645,7 @@ extern "C" int mdx_gemm_tc_pick_block_n(int32_t N, int32_t geglu) {
     return 0;
   }
   if (N % 160 == 0) return 160;
+  if (N % 192 == 0) return 192;   // GLIDE's channel counts (192, 384, 576, 768): one to four full tiles
   if (N % 128 == 0) return 128;
   if (N % 64 == 0) return 64;
   // fewest padded columns, ties to the larger tile
@@ -711,7 +712,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     ktot += (long long)a->seg_taps[s] * a->seg_c[s];
   }
   int bn = a->block_n ? a->block_n : mdx_gemm_tc_pick_block_n(a->N, a->geglu);
-  MDX_CHECK_ARG(bn == 64 || bn == 128 || bn == 160 || bn == 256, "mdx_gemm_tc: unsupported block_n %d", bn);
+  MDX_CHECK_ARG(bn == 64 || bn == 128 || bn == 160 || bn == 192 || bn == 256, "mdx_gemm_tc: unsupported block_n %d", bn);
   if (a->geglu) MDX_CHECK_ARG((a->N / 2) % (bn / 2) == 0, "mdx_gemm_tc: geglu needs N/2 %% (block_n/2) == 0");
 
   p.n_img = a->n_img; p.H = a->H; p.W = a->W;
@@ -764,6 +765,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     case 64: return launch_tc<64>(maps, mb, p, st);
     case 128: return launch_tc<128>(maps, mb, p, st);
     case 160: return launch_tc<160>(maps, mb, p, st);
+    case 192: return launch_tc<192>(maps, mb, p, st);
     default: return launch_tc<256>(maps, mb, p, st);
   }
 }

@@ -685,8 +685,12 @@ class SuperResText2ImUNet(Text2ImUNet):
         """low_res: fp32 NCHW [B, 3, h, w] -> the conditioning channels, resized to image_size (text2im_model.py:191).
         quantize_u8 applies PMeanVariance.superResPreprocess first (the sampler's path)."""
         low = low_res.to(device=self.device, dtype=torch.float32).contiguous()
-        self._low_up = ops.resize_bilinear(low, self.image_size, self.image_size, quantize_u8)
-        self._graphs = {}
+        up = ops.resize_bilinear(low, self.image_size, self.image_size, quantize_u8)
+        if self._low_up is not None and self._low_up.shape == up.shape:
+            self._low_up.copy_(up)   # same shape: refill the buffer the captured graphs read
+        else:
+            self._low_up = up
+            self._graphs = {}
 
     def __call__(self, x, timesteps, low_res=None, tokens=None, mask=None):
         self.set_low_res(low_res)

@@ -56,7 +56,7 @@ def test_gemm_tc_dense(M, K, N):
     assert rel_err(out32, a @ w.t()) < 1e-4
 
 
-@pytest.mark.parametrize("bn", [64, 128, 160, 256])
+@pytest.mark.parametrize("bn", [64, 128, 160, 192, 256])
 def test_gemm_tc_block_n_variants(bn):
     ops = _ops()
     g = torch.Generator().manual_seed(bn)
