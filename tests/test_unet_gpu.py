@@ -274,3 +274,37 @@ def test_hybrid_conditioning_inpainting_shape(dtype, tol):
     with pytest.raises(ValueError):
         model.set_concat(None)
         model(x_T.cuda(), t.cuda(), context=c.cuda())                     # 4 channels into a 9-channel UNet
+
+
+def test_sd2_full_size_50_step_ddim_final_latents():
+    """The north star's end criterion at the bench's own shape: SD2 512-base UNet, 64x64 latent, 50-step DDIM,
+    CFG 7.5.  The CPU oracle cannot run 100 full-size evaluations in test time, so the chain is anchored in two links:
+    (1) ONE full-size guided evaluation of the fp32 check mode against the CPU oracle, <= 1e-4 (and the bf16 path on
+    the same inputs, <= 1.25e-2: single-draw allowance of the 1e-2 mean criterion, see test_tiny_unet_eps);
+    (2) all 50 steps, bf16 product path against the fp32 check mode on the GPU: final latents cosine >= 0.999."""
+    from minddiffusion_b200 import samplers
+    from minddiffusion_b200.unet import UNetModel
+    from minddiffusion_b200.weights import random_unet_params
+    from oracle import sd_unet
+    cfg = sd_unet.SD2_UNET
+    P = random_unet_params(cfg, 0)
+    x_T = torch.from_numpy(np.random.RandomState(42).randn(1, 4, 64, 64).astype(np.float32))
+    c = torch.from_numpy(np.random.RandomState(43).randn(1, 77, 1024).astype(np.float32))
+    uc = torch.from_numpy(np.random.RandomState(44).randn(1, 77, 1024).astype(np.float32))
+    t = torch.full((2,), 981.0)
+    Pt = {k: torch.from_numpy(v) for k, v in P.items()}
+    ref = sd_unet.unet_forward(Pt, cfg, torch.cat((x_T, x_T)), t, torch.cat((uc, c)))
+    out = {}
+    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 1.25e-2)):
+        model = UNetModel(P, dtype=dtype, **cfg)
+        model.set_context(torch.cat((uc, c), 0).cuda())
+        e = model.forward_nhwc(x_T.cuda(), t.cuda(), repeat=2)[..., :4].permute(0, 3, 1, 2)
+        assert rel_err(e, ref) <= tol, (dtype, rel_err(e, ref))
+        model.use_cuda_graph = True
+        out[dtype], _ = samplers.DDIMSampler(_ldm(model)).sample(
+            50, 1, (4, 64, 64), c.cuda(), x_T=x_T.cuda(), verbose=False, unconditional_guidance_scale=7.5,
+            unconditional_conditioning=uc.cuda(), eta=0.0)
+        del model
+        torch.cuda.empty_cache()
+    assert torch.isfinite(out[torch.bfloat16]).all()
+    assert cosine(out[torch.bfloat16], out[torch.float32]) >= 0.999
