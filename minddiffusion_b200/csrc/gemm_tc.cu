@@ -101,7 +101,8 @@ __device__ __forceinline__ float4 epi_load_add(const TcParams& p, long long pix,
 
 template <int BN, bool OUT_F32, bool HAS_ADD>
 __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint32_t stg, int lane, int cpar,
-                                         int cstep, int n_tile, long long pix_own, long long stat_slot) {
+                                         int cstep, int n_tile, long long pix_own, long long stat_slot,
+                                         uint64_t* tfull_bar, uint32_t tfull_parity) {
   const int n_out = p.N;
   const int ocol_tile = n_tile * BN;
   const int sr8 = lane >> 2, q4 = lane & 3;
@@ -110,6 +111,8 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
   for (int pass = 0; pass < 4; ++pass) pix8[pass] = __shfl_sync(0xffffffffu, pix_own, pass * 8 + sr8);
   if constexpr (!OUT_F32 && !HAS_ADD) {
     constexpr int NCH = BN / 32;
+    mbar_wait(tfull_bar, tfull_parity);
+    tc_fence_after();
 #pragma unroll 1
     for (int c = cpar; c < NCH; c += cstep) {
       const int ocol0 = ocol_tile + c * 32;
@@ -154,16 +157,25 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
     }
   } else {
     constexpr int NCH = BN / 16;
-    float4 radd[4];
-    if constexpr (HAS_ADD) {   // residual (+ per-image bias) of this warp's first chunk
-      const int col = ocol_tile + cpar * 16 + q4 * 4;
+    // residual (+ per-image bias) of this warp's first TWO chunks, requested before the accumulator is even ready:
+    // nothing here depends on the MMAs, and two chunks in flight per warp keep enough bytes outstanding for HBM
+    float4 radd[4], rnext[4];
+    auto load_add = [&](float4 (&dst)[4], int c) {
+      const int col = ocol_tile + c * 16 + q4 * 4;
+      const bool ok = c < NCH && col < n_out;
 #pragma unroll
       for (int pass = 0; pass < 4; ++pass) {
-        radd[pass] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (cpar < NCH && col < n_out && pix8[pass] >= 0)
-          radd[pass] = p.res_f32 ? epi_load_add<true>(p, pix8[pass], col) : epi_load_add<false>(p, pix8[pass], col);
+        dst[pass] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok && pix8[pass] >= 0)
+          dst[pass] = p.res_f32 ? epi_load_add<true>(p, pix8[pass], col) : epi_load_add<false>(p, pix8[pass], col);
       }
+    };
+    if constexpr (HAS_ADD) {
+      load_add(radd, cpar);
+      load_add(rnext, cpar + cstep);
     }
+    mbar_wait(tfull_bar, tfull_parity);
+    tc_fence_after();
 #pragma unroll 1
     for (int c = cpar; c < NCH; c += cstep) {
       const int ocol0 = ocol_tile + c * 16;
@@ -172,17 +184,8 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
       const bool col_ok = col < n_out;
       uint32_t r[16];
       tmem_ld16(taddr + c * 16, r);
-      float4 rnext[4];
-      if constexpr (HAS_ADD) {   // next chunk's loads fly while this chunk is transposed and stored
-        const int coln = col + cstep * 16;
-        const bool nok = (c + cstep) < NCH && coln < n_out;
-#pragma unroll
-        for (int pass = 0; pass < 4; ++pass) {
-          rnext[pass] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (nok && pix8[pass] >= 0)
-            rnext[pass] = p.res_f32 ? epi_load_add<true>(p, pix8[pass], coln) : epi_load_add<false>(p, pix8[pass], coln);
-        }
-      }
+      float4 rnext2[4];
+      if constexpr (HAS_ADD) load_add(rnext2, c + 2 * cstep);   // two chunks ahead
       float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
       if (col_ok && p.bias) bz = __ldg(reinterpret_cast<const float4*>(p.bias + col));
       tmem_ld_wait();
@@ -240,7 +243,7 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
       }
       if constexpr (HAS_ADD) {
 #pragma unroll
-        for (int pass = 0; pass < 4; ++pass) radd[pass] = rnext[pass];
+        for (int pass = 0; pass < 4; ++pass) { radd[pass] = rnext[pass]; rnext[pass] = rnext2[pass]; }
       }
     }
   }
@@ -417,8 +420,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                                 : (p.up ? ((long long)n * 2 * p.H + 2 * y + p.up_py) * (2 * p.W) + 2 * x + p.up_px
                                         : ((long long)n * p.H + y) * p.W + x);
 
-      mbar_wait(&tfull[as], aph);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + as * BN;
       // statistics slot of this warp's 32 rows: (image, [phase,] tile inside the image, lane quadrant); tn == 1
       long long stat_slot = -1;
@@ -429,8 +430,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       }
 
       if (p.debug & 2) {
-        // profiling only: drop the tile
+        mbar_wait(&tfull[as], aph);  // profiling only: drop the tile
       } else if (p.geglu) {
+        mbar_wait(&tfull[as], aph);
+        tc_fence_after();
         // GEGLU: the tile holds [BN/2 value columns | the matching BN/2 gate columns].  In the row-owner layout a
         // thread forms (value + bv) * gelu(gate + bg) for up to 32 output columns of its row, packs bf16, and the
         // unit goes through the 80-byte-row staging tile to 16-byte coalesced stores (as the plain bf16 path).
@@ -499,11 +502,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           }
         }
       } else if (p.out_f32) {
-        if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
-        else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
+        if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
+        else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
       } else {
-        if (has_add) epi_tile<BN, false, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
-        else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot);
+        if (has_add) epi_tile<BN, false, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
+        else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
       }
       tc_fence_before();
       mbar_arrive(&tempty[as]);
