@@ -12,6 +12,7 @@ import numpy as np
 import torch
 
 from . import ops
+from .unet import fold_upsample_weights, upsample_conv3x3
 
 PREFIX = "first_stage_model."
 
@@ -144,7 +145,11 @@ class AutoencoderKL:
                 for t in ("q", "k", "v", "proj_out"):
                     self.L[nm + "." + t] = (w(g(d + nm + "." + t + ".weight").reshape(c, c)), g(d + nm + "." + t + ".bias"))
             elif l[0] == "up":
-                self.L[l[1]] = (w(ck(g(d + l[1] + ".conv.weight"))), g(d + l[1] + ".conv.bias"))
+                if self.bf16:  # nearest x2 + conv3x3 as four 2x2 phase GEMMs over the source image (unet.py)
+                    self.L[l[1]] = ([w(wp) for wp in fold_upsample_weights(g(d + l[1] + ".conv.weight"))],
+                                    g(d + l[1] + ".conv.bias"))
+                else:
+                    self.L[l[1]] = (w(ck(g(d + l[1] + ".conv.weight"))), g(d + l[1] + ".conv.bias"))
             elif l[0] == "out":
                 self.L["norm_out"] = (g(d + "norm_out.gamma"), g(d + "norm_out.beta"))
                 cw, cb = ck(g(d + "conv_out.weight")), g(d + "conv_out.bias")
@@ -165,12 +170,20 @@ class AutoencoderKL:
         return v.to(device=self.device, dtype=torch.float32).contiguous()
 
     # ---- op helpers ----
+    def _chan(self, n, H, W, C, up=False):
+        """Slot buffer for the GroupNorm statistics a GEMM epilogue collects for its consumer (see UNetModel._chan)."""
+        slots = ops.stat_slots(n, H, W, up)
+        return torch.empty((n, slots, 2, C), dtype=torch.float32, device=self.device) if slots else None
+
     def _conv3(self, x, w, b, residual=None, skips=None, trunk=False):
         n, H, W, _ = x.shape
         if self.bf16:
             segs = [(x, 9)] + [(s, 1) for s in (skips or [])]
-            return ops.gemm_tc(segs, w, bias=b, residual=residual,
-                               out_dtype=torch.float32 if trunk else torch.bfloat16).view(n, H, W, -1)
+            chan = self._chan(n, H, W, w.shape[0])
+            out = ops.gemm_tc(segs, w, bias=b, residual=residual, chan_stats=chan,
+                              out_dtype=torch.float32 if trunk else torch.bfloat16).view(n, H, W, -1)
+            out._mdx_chan = chan
+            return out
         return ops.conv_direct(x, w, 3, 3, 1, 1, bias=b, residual=residual)
 
     def _dense(self, x2, w, b=None, residual=None, trunk=False):
@@ -184,11 +197,13 @@ class AutoencoderKL:
         g1, b1 = L[nm + ".n1"]
         raw = None
         if self.bf16 and cin != cout:
-            h, raw = ops.groupnorm(x, g1, b1, 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt, raw_copy=True)
+            h, raw = ops.groupnorm(x, g1, b1, 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt, raw_copy=True,
+                                   chan1=getattr(x, "_mdx_chan", None))
         else:
-            h = ops.groupnorm(x, g1, b1, 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt)
+            h = ops.groupnorm(x, g1, b1, 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt,
+                              chan1=getattr(x, "_mdx_chan", None))
         h = self._conv3(h, *L[nm + ".c1"])
-        h = ops.groupnorm(h, *L[nm + ".n2"], 32, 1e-6, silu=True, scratch=self._scr)
+        h = ops.groupnorm(h, *L[nm + ".n2"], 32, 1e-6, silu=True, scratch=self._scr, chan1=getattr(h, "_mdx_chan", None))
         w2, b2 = L[nm + ".c2"]
         if cin == cout:
             return self._conv3(h, w2, b2, residual=x, trunk=True)
@@ -240,11 +255,14 @@ class AutoencoderKL:
             elif l[0] == "up":
                 wu, bu = L[l[1]]
                 if self.bf16:
-                    x = self._conv3(ops.upsample_nearest2x(x, out_dtype=dt), wu, bu, trunk=True)
+                    chan = self._chan(x.shape[0], x.shape[1], x.shape[2], wu[0].shape[0], up=True)
+                    x = upsample_conv3x3(ops.cast(x, dt), wu, bu, torch.float32, chan)
+                    x._mdx_chan = chan
                 else:
                     x = ops.conv_direct(x, wu, 3, 3, 1, 1, upsample=True, bias=bu)
             elif l[0] == "out":
-                hh = ops.groupnorm(x, *L["norm_out"], 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt)
+                hh = ops.groupnorm(x, *L["norm_out"], 32, 1e-6, silu=True, scratch=self._scr, out_dtype=dt,
+                                   chan1=getattr(x, "_mdx_chan", None))
                 wo, bo = L["conv_out"]
                 n, H, W, _ = hh.shape
                 if self.bf16:
