@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--cfg-split", action="store_true",
                     help="N >= 2: split the cond/uncond halves of each batch across GPU pairs (per-step eps exchange)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-pair-split", action="store_true", help="N >= 2: skip the CFG pair-split measurement")
     return ap.parse_args()
 
 
@@ -167,6 +168,70 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel's largest shape, from the
+# `ncu --set full` capture named in the note (a profiler number, copied here; everything else in the line is live)
+TRAFFIC = {"bytes_per_launch": 634.0e6,
+           "note": "ncu --set full, gemm_tc_kernel conv3x3 C=320 at 64x64, CFG batch 128 (M=524288, N=320, K=2880): "
+                   "634 MB DRAM traffic vs 673 MB algorithmic (A once + out once; weights from L2) — no re-reads; "
+                   "profiles/r01_ncu_full_gemm_tc_conv3x3_c320_raw.csv"}
+
+
+def hbm_probe(torch, ops, dev, B, h, hbm_peak):
+    """Achieved HBM GB/s of the memory-bound kernels at the workload's shapes: algorithmic bytes / CUDA-event time of
+    single launches, L2 flushed (a 512 MB fill) before each one.  The sampler kernels' tensors are small (25 MB at
+    batch 64), so inside the real step they mostly hit L2; this is the cold figure."""
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+
+    def time_one(fn, reps=5):
+        best = 1e30
+        for _ in range(reps):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best
+
+    out = {}
+    n = 2 * B
+    x = torch.randn(B, 4, h, h, device=dev)
+    eps = torch.randn(n, h, h, 16, device=dev)
+    row = ops.plms_coef_row((1., 0., 0., 0.), (0.5, 0.6, 0.0, 0.70710678))
+    xo, p0 = torch.empty_like(x), torch.empty_like(x)
+    nb = x.numel() * 4
+    cases = [("plms_step_kernel (DDIM: eps_u, eps_c, x -> x_prev, pred_x0)", 5 * nb,
+              lambda: ops.sampler_step_ex("plms", eps, x, xo, 4, True, 7.5, row=row, pred_x0=p0)),
+             ("dpm_step_kernel (eps_u, eps_c, x, x0_prev -> x, x0)", 6 * nb,
+              lambda: ops.sampler_step_ex("dpm", eps, x, xo, 4, True, 7.5, row=[0.9, 0.4, 1.0, 0.1, 0.05, 1.0] + [0.0] * 10,
+                                          hist=(p0, None, None), pred_x0=p0))]
+    C = 320
+    a32 = torch.randn(n, h, h, C, device=dev)
+    a16 = a32.to(torch.bfloat16)
+    g, b_ = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    rows = n * h * h
+    o16 = torch.empty(n, h, h, C, dtype=torch.bfloat16, device=dev)
+    scratch = torch.empty(n * 64, dtype=torch.float64, device=dev)
+    chan = torch.zeros((n, ops.stat_slots(n, h, h), 2, C), device=dev)
+    chan[:, :, 1] = 1.0
+    cases += [("gn_apply_kernel fp32->bf16 + SiLU (C=320, 64x64)", rows * C * 6,
+               lambda: ops.groupnorm(a32, g, b_, 32, 1e-5, silu=True, out=o16, scratch=scratch, chan1=chan)),
+              ("gn_apply_kernel bf16->bf16 + SiLU (C=320, 64x64)", rows * C * 4,
+               lambda: ops.groupnorm(a16, g, b_, 32, 1e-5, silu=True, out=o16, scratch=scratch, chan1=chan)),
+              ("layernorm_kernel fp32->bf16 (C=320)", rows * C * 6,
+               lambda: ops.layernorm(a32.view(rows, C), g, b_, out=o16.view(rows, C)))]
+    for name, nbytes, fn in cases:
+        fn()
+        ms = time_one(fn)
+        gbs = nbytes / (ms / 1e3) / 1e9
+        out[name] = {"GB/s": round(gbs, 1), "frac_of_hbm_peak": round(gbs / hbm_peak, 3), "us": round(ms * 1e3, 1),
+                     "algorithmic_MB": round(nbytes / 1e6, 1)}
+    out["note"] = ("gn_apply includes its gn_fold launch (statistics arrive from the producer's epilogue); "
+                   "peak %.1f GB/s = MEASURED_PEAKS.json copy bandwidth" % hbm_peak)
+    return out
+
+
 def run_b200(a):
     import numpy as np
     import torch
@@ -256,12 +321,48 @@ def run_b200(a):
     value = images / (ms / 1e3)
     e2e = images / (ms_e2e / 1e3)
 
+    # ---- N >= 2, same run: CFG pair split (BASELINE config #3).  GPU 2k evaluates the unconditional half of a batch
+    #      of B prompts, GPU 2k+1 the conditional half; each step the 4-channel eps halves are exchanged with one NCCL
+    #      all-gather issued INSIDE the captured step graph and both ranks apply the same update. ----
+    pair = None
+    if world >= 2 and world % 2 == 0 and not a.cfg_split and not a.no_pair_split:
+        from minddiffusion_b200.parallel import CfgPairSplit
+        ldm.cfg_split = split = CfgPairSplit()
+        xp = torch.from_numpy(np.random.RandomState(42 + rank // 2).randn(B, *shape).astype(np.float32)).to(dev)
+        step_pair = lambda: sampler.sample(S, B, shape, c_dev, x_T=xp, verbose=False, eta=0.0,
+                                           unconditional_guidance_scale=a.scale, unconditional_conditioning=uc_dev)[0]
+        lat = step_pair()                                       # warm-up: captures the pair-split step graph
+        both = [torch.empty_like(lat) for _ in range(2)]
+        dist.all_gather(both, lat, group=split.group)
+        identical = bool(torch.equal(both[0], both[1]))        # the two ranks of a pair hold the same latents
+        kp = max(1, min(a.steps, 3))
+        ms_pair = timed(step_pair, kp)
+        probe = torch.randn(B, h, h, 16, device=dev)
+        for _ in range(3):
+            split.exchange(probe, channels=4)
+        barrier()
+        x0e, x1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        x0e.record()
+        for _ in range(20):
+            split.exchange(probe, channels=4)
+        x1e.record()
+        barrier()
+        pair = {"value": B * (world // 2) * kp / (ms_pair / 1e3), "unit": "images/s", "steps": kp,
+                "ms_per_unet_eval": ms_pair / kp / S, "dp_ms_per_unet_eval": ms / a.steps / S,
+                "exchange_us": x0e.elapsed_time(x1e) * 1e3 / 20, "exchange_bytes_per_rank": B * h * h * 4 * 4,
+                "latents_identical_on_pair": identical, "in_graph": not a.no_graph,
+                "parallelism": "dp%d x cfg-pair-split (packed 4-channel eps all-gather over NCCL inside the step graph)"
+                               % (world // 2)}
+        ldm.cfg_split = None
+
     # ---- dominant kernel, live: every mdx_gemm_tc launch of one guided UNet evaluation ----
     prof = []
     ops.GEMM_TC_PROFILE = prof
     unet.use_cuda_graph = False
     rep = 1 if a.cfg_split else 2
     t_probe = torch.full((rep * B,), 501.0, device=dev)
+    if rep == 2:
+        unet.set_context(torch.cat((uc_dev, c_dev), 0))   # the pair-split phase left a single-branch context behind
     unet.forward_nhwc(x_dev, t_probe, repeat=rep)
     torch.cuda.synchronize()
     ops.GEMM_TC_PROFILE = None
@@ -273,8 +374,11 @@ def run_b200(a):
     except (OSError, ValueError):
         pass
     peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    peak_burst = float(peaks.get("bf16_tflops", 1650.0))
+    hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
     peak_kind = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md, sustained)"
     achieved = flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
+    hbm_kernels = hbm_probe(torch, ops, dev, B, h, hbm_peak) if world == 1 else None
     fwd_flops = FLOP_PER_SAMPLE_FWD_SD2_64 * (h / 64.0) ** 2  # conv/linear scale ~ pixels; attention differs slightly
     step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None  # per GPU
 
@@ -308,10 +412,16 @@ def run_b200(a):
         "unet_tflops_per_gpu": step_tflops,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (mdx_gemm_tc: conv3x3 / 1x1 / dense)",
                      "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-                     "peak_kind": peak_kind, "traffic": None, "launches": len(prof), "kernel_ms_per_unet_eval": gemm_ms,
-                     "whole_step_frac": (step_tflops / peak) if step_tflops else None},
+                     "peak_kind": peak_kind, "frac_of_burst_peak": achieved / peak_burst, "peak_burst": peak_burst,
+                     "traffic": TRAFFIC["bytes_per_launch"], "traffic_note": TRAFFIC["note"],
+                     "launches": len(prof), "kernel_ms_per_unet_eval": gemm_ms,
+                     "whole_step_frac": (step_tflops / peak) if step_tflops else None,
+                     "whole_step_frac_of_burst_peak": (step_tflops / peak_burst) if step_tflops else None},
+        "hbm_kernels": hbm_kernels,
         "cpu_baseline": cpu,
     }
+    if pair is not None:
+        line["pair_split"] = pair
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -267,6 +267,70 @@ int mdx_sampler_dpmpp2m_step(const void* eps_model, int64_t ld_eps, int32_t mode
                              void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * Struct form of the two step kernels above, with three additions:
+ *  (1) per-step scalars either from the host (coef_host, one row) or from a DEVICE table coef_table[rows][MDX_STEP_COEFS]
+ *      indexed by the device counter *step_dev — a step's launches are then identical from step to step, so the whole
+ *      step (UNet + this kernel + mdx_step_advance) is captured once in a CUDA graph and replayed (the host loop of
+ *      plms.py:146-177 / dpm_solver.py:1073-1094 only replays);
+ *  (2) model_type 1 ("v") for the PLMS / DDIM update too: e_t = row[9] * out + row[10] * x_model, the conversion
+ *      model_wrapper applies (dpm_solver.py:281-284) with (row[9], row[10]) = (sqrt(abar_t), sqrt(1 - abar_t)) of the
+ *      timestep the model was evaluated at and x_model the latent it was evaluated on (NULL = x);
+ *  (3) shift_hist: the PLMS eps history is advanced inside the kernel (hist3 <- hist2 <- hist1 <- e_t, plms.py:168-170)
+ *      so the buffers keep their addresses across steps; unused history must be zero-filled, not uninitialised.
+ * Rows (MDX_STEP_COEFS floats, unused entries 0):
+ *   PLMS/DDIM  {w0, w1, w2, w3, sqrt(a_t), sqrt(a_prev), sqrt(1 - a_prev - sigma^2), sigma, sqrt(1 - a_t), v_a, v_s,
+ *               use_noise} — fill with mdx_sampler_plms_coef_row (host; the arithmetic mdx_sampler_plms_step uses)
+ *   DPM++(2M)  {alpha_s, sigma_s, c_x, c_0, c_1, use_prev}   (use_prev 0 = first-order update: hist[0] is not read)
+ * hist[0..2]: PLMS old eps 1..3 (may be NULL without shift_hist); DPM: hist[0] = x0_prev, pred_x0 = x0_cur (may alias).
+ * x_out may alias x.
+ * --------------------------------------------------------------------------------------------------------- */
+#define MDX_STEP_COEFS 16
+typedef struct mdx_step_args {
+  const void* model_out;
+  int64_t ld_out;
+  int32_t model_dtype;
+  int32_t cfg;
+  float scale;
+  int32_t model_type;
+  const float* x;
+  const float* x_model;
+  float* hist[3];
+  const float* noise;
+  float* x_out;
+  float* pred_x0;
+  float* e_t_out;
+  int32_t shift_hist;
+  int32_t B, C, h, w;
+  const float* coef_host;
+  const float* coef_table;
+  const int32_t* step_dev;
+} mdx_step_args;
+int mdx_sampler_plms_step_ex(const mdx_step_args* args, void* stream);
+int mdx_sampler_dpmpp2m_step_ex(const mdx_step_args* args, void* stream);
+/* Host helper: w4 = AB weights, coef4 = {a_t, a_prev, sigma_t, sqrt_one_minus_a_t} (as mdx_sampler_plms_step),
+ * v2 = {v_a, v_s} or NULL (eps model) -> row[MDX_STEP_COEFS]. */
+int mdx_sampler_plms_coef_row(const float* w4_host, const float* coef4_host, const float* v2_host, int32_t use_noise,
+                              float* row_host);
+/* *step_dev += delta (one thread; the last launch of a captured step). */
+int mdx_step_advance(int32_t* step_dev, int32_t delta, void* stream);
+/* out[j][0..width) = table[*idx_dev + offset][0..width) for j < n_out (table row stride ld): the timestep vector of
+ * the step (plms.py:148 `ts = full((b,), step)`) read from a device table inside a captured step. */
+int mdx_gather_row(const float* table, int64_t ld, const int32_t* idx_dev, int32_t offset, float* out, int32_t n_out,
+                   int32_t width, void* stream);
+/* Inpainting blend of the sampler loop (wukong-huahua plms.py:153-156 with q_sample, ddpm.py:180-182):
+ *   img = (sqrt_ac * x0 + sqrt_1m_ac * noise) * mask + (1 - mask) * img, in place.
+ * x0, noise, img: fp32 NCHW [B, C, h, w]; mask: fp32 [B, mask_channels, h, w], mask_channels 1 (broadcast) or C. */
+int mdx_sampler_mask_blend(const float* x0, const float* noise, const float* mask, int32_t mask_channels, float sqrt_ac,
+                           float sqrt_1m_ac, float* img, int32_t B, int32_t C, int32_t h, int32_t w, void* stream);
+
+/* Struct sizes as this library was compiled — a binding compares them with its own declaration before the first call
+ * (a short struct would make the library read fields from whatever follows it in memory). */
+int32_t mdx_sizeof_gemm_args(void);
+int32_t mdx_sizeof_conv_args(void);
+int32_t mdx_sizeof_step_args(void);
+int32_t mdx_offsetof_gemm_args_chan_stats(void);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Taichu-GLIDE family (vision/Taichu-GLIDE/model/glide_text2im): the operators its UNet / sampler need beyond
  * the latent-diffusion set above.
  *

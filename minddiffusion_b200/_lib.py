@@ -59,6 +59,21 @@ class ConvArgs(ctypes.Structure):
     ]
 
 
+class StepArgs(ctypes.Structure):
+    _fields_ = [
+        ("model_out", c_p), ("ld_out", c_i64), ("model_dtype", c_int), ("cfg", c_int), ("scale", c_f),
+        ("model_type", c_int),
+        ("x", c_p), ("x_model", c_p),
+        ("hist", c_p * 3),
+        ("noise", c_p), ("x_out", c_p), ("pred_x0", c_p), ("e_t_out", c_p),
+        ("shift_hist", c_int),
+        ("B", c_int), ("C", c_int), ("h", c_int), ("w", c_int),
+        ("coef_host", c_p), ("coef_table", c_p), ("step_dev", c_p),
+    ]
+
+
+STEP_COEFS = 16
+
 # name -> (restype, argtypes); must list every symbol include/mdx.h declares (tests check this)
 SIGNATURES = {
     "mdx_last_error": (ctypes.c_char_p, []),
@@ -103,6 +118,16 @@ SIGNATURES = {
                                       c_p]),
     "mdx_prelu": (c_int, [c_p, c_i64, c_i64, c_int, c_p, c_p, c_i64, c_p, c_i64, c_int, c_int, c_p]),
     "mdx_depth_to_space2": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p, c_p, c_int, c_int, c_p]),
+    "mdx_sampler_plms_step_ex": (c_int, [ctypes.POINTER(StepArgs), c_p]),
+    "mdx_sampler_dpmpp2m_step_ex": (c_int, [ctypes.POINTER(StepArgs), c_p]),
+    "mdx_sampler_plms_coef_row": (c_int, [c_p, c_p, c_p, c_int, c_p]),
+    "mdx_step_advance": (c_int, [c_p, c_int, c_p]),
+    "mdx_gather_row": (c_int, [c_p, c_i64, c_p, c_int, c_p, c_int, c_int, c_p]),
+    "mdx_sampler_mask_blend": (c_int, [c_p, c_p, c_p, c_int, c_f, c_f, c_p, c_int, c_int, c_int, c_int, c_p]),
+    "mdx_sizeof_gemm_args": (c_int, []),
+    "mdx_sizeof_conv_args": (c_int, []),
+    "mdx_sizeof_step_args": (c_int, []),
+    "mdx_offsetof_gemm_args_chan_stats": (c_int, []),
     "mdx_sampler_glide_step": (c_int, [c_p, c_i64, c_int, c_int, c_f, c_int, c_p, c_p, c_p, c_p, c_p, c_int, c_int,
                                        c_int, c_int, c_p]),
 }
@@ -127,6 +152,12 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
+    # the ctypes mirrors of the argument structs must match the compiled header byte for byte
+    for name, cls in (("gemm", GemmArgs), ("conv", ConvArgs), ("step", StepArgs)):
+        want = getattr(lib, "mdx_sizeof_%s_args" % name)()
+        if ctypes.sizeof(cls) != want:
+            raise MdxError("struct mdx_%s_args is %d bytes in the library, %d in the binding" %
+                           (name, want, ctypes.sizeof(cls)))
     _lib = lib
     return lib
 

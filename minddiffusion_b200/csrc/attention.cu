@@ -268,10 +268,10 @@ template <int HD>
 int launch_fa(const AttnP& p, cudaStream_t st) {
   constexpr int LDS = HD + 8;
   constexpr int SMEM = (FA_BM + 4 * FA_BN) * LDS * 2;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static MdxPerDeviceOnce attr;
+  if (attr.need()) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(flash_attn_bf16_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_set = true;
+    attr.mark();
   }
   dim3 grid((p.Nq + FA_BM - 1) / FA_BM, p.heads, p.batch);
   flash_attn_bf16_kernel<HD><<<grid, 256, SMEM, st>>>(p);

@@ -572,11 +572,11 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
   if ((rc = make_map_qkv(&mq, q, ldq, d, heads, Nq, batch))) return rc;
   if ((rc = make_map_qkv(&mk, k, ldk, d, heads, Nk, batch))) return rc;
   if ((rc = make_map_qkv(&mv, v, ldv, d, heads, Nk, batch))) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static MdxPerDeviceOnce attr;
+  if (attr.need()) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT1_SMEM));
-    attr_set = true;
+    attr.mark();
   }
   AttnTcP p;
   p.Nq = Nq; p.Nk = Nk; p.sl2 = scale * 1.4426950408889634f;

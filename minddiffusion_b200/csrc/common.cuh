@@ -41,6 +41,34 @@ void mdx_set_error(const char* fmt, ...);
 
 typedef __nv_bfloat16 bf16;
 
+// Kernel attributes (the shared-memory opt-in) and the SM count belong to a DEVICE, not to the process: launch code
+// keeps one flag / value per device ordinal, looked up with the current device.
+constexpr int MDX_MAX_DEVICES = 64;
+struct MdxPerDeviceOnce {
+  bool done[MDX_MAX_DEVICES] = {};
+  // true exactly when the caller still has to run its per-device set-up (benign if two threads race: both run it)
+  bool need() const {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= MDX_MAX_DEVICES) return true;
+    return !done[d];
+  }
+  void mark() {
+    int d = 0;
+    if (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < MDX_MAX_DEVICES) done[d] = true;
+  }
+};
+inline int mdx_num_sms() {
+  static int sms[MDX_MAX_DEVICES] = {};
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= MDX_MAX_DEVICES) return 148;
+  if (!sms[d]) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d) != cudaSuccess || v <= 0) v = 148;
+    sms[d] = v;
+  }
+  return sms[d];
+}
+
 // ----------------------------------------------------------------------------------------------
 // dtype helpers for kernels templated on float / bf16 storage (fp32 "check mode" vs bf16 mode)
 // ----------------------------------------------------------------------------------------------
@@ -52,6 +80,14 @@ template <> __device__ __forceinline__ float from_f32<float>(float v) { return v
 template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
+// x * sigmoid(x) on the SFU's ex2 and rcp (relative error ~2e-7, no division sequence): the form the bf16-output
+// passes use, where the IEEE divide of silu_f made GroupNorm+SiLU compute-bound instead of HBM-bound
+__device__ __forceinline__ float silu_fast(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+  return x * r;
+}
 // MindSpore ops.GeLU / nn.GELU() default = tanh approximation (reference attention.py:46)
 __device__ __forceinline__ float gelu_tanh_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;

@@ -157,9 +157,15 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
     }
   } else {
     constexpr int NCH = BN / 16;
-    // residual (+ per-image bias) of this warp's first TWO chunks, requested before the accumulator is even ready:
-    // nothing here depends on the MMAs, and two chunks in flight per warp keep enough bytes outstanding for HBM
-    float4 radd[4], rnext[4];
+    constexpr int CSTEP = TcCfg<BN>::EPI_WARPS / 4;            // == cstep
+    constexpr int MAXC = (NCH + CSTEP - 1) / CSTEP;            // chunks one warp can own in a tile (<= 6)
+    constexpr int NBUF = MAXC < 4 ? MAXC : 4;
+    // Residual (+ per-image bias) operands: the loads of ALL of this warp's chunks of the tile (up to four; the rest
+    // as buffers free up) are issued before the accumulator is even ready — nothing here depends on the MMAs, and a
+    // whole tile's worth of bytes in flight per SM is what keeps HBM busy.  The chunk loop is fully unrolled so every
+    // buffer is a fixed set of registers: rotating buffers with register moves would make each move wait for the load
+    // it copies, which serialises the loads again.
+    float4 radd[NBUF][4];
     auto load_add = [&](float4 (&dst)[4], int c) {
       const int col = ocol_tile + c * 16 + q4 * 4;
       const bool ok = c < NCH && col < n_out;
@@ -171,21 +177,20 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
       }
     };
     if constexpr (HAS_ADD) {
-      load_add(radd, cpar);
-      load_add(rnext, cpar + cstep);
+#pragma unroll
+      for (int k = 0; k < NBUF; ++k) load_add(radd[k], cpar + k * CSTEP);
     }
     mbar_wait(tfull_bar, tfull_parity);
     tc_fence_after();
-#pragma unroll 1
-    for (int c = cpar; c < NCH; c += cstep) {
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = cpar + k * CSTEP;
       const int ocol0 = ocol_tile + c * 16;
-      if (ocol0 >= n_out) break;
+      if (c >= NCH || ocol0 >= n_out) continue;                 // warp-uniform
       const int col = ocol0 + q4 * 4;
       const bool col_ok = col < n_out;
       uint32_t r[16];
       tmem_ld16(taddr + c * 16, r);
-      float4 rnext2[4];
-      if constexpr (HAS_ADD) load_add(rnext2, c + 2 * cstep);   // two chunks ahead
       float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
       if (col_ok && p.bias) bz = __ldg(reinterpret_cast<const float4*>(p.bias + col));
       tmem_ld_wait();
@@ -202,7 +207,10 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
         if (p.act) {  // activation sits between the bias and the residual
           o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act);
         }
-        if constexpr (HAS_ADD) { o.x += radd[pass].x; o.y += radd[pass].y; o.z += radd[pass].z; o.w += radd[pass].w; }
+        if constexpr (HAS_ADD) {
+          const float4 a4 = radd[k % NBUF][pass];
+          o.x += a4.x; o.y += a4.y; o.z += a4.z; o.w += a4.w;
+        }
         const long long pix = pix8[pass];
         if (!col_ok || pix < 0 || (p.debug & 1)) continue;
         if constexpr (OUT_F32) {
@@ -223,16 +231,19 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
           cq[2] = fmaf(o.z, o.z, cq[2]); cq[3] = fmaf(o.w, o.w, cq[3]);
         }
       }
+      if constexpr (HAS_ADD) {
+        if (k + NBUF < MAXC) load_add(radd[k % NBUF], cpar + (k + NBUF) * CSTEP);   // this buffer is free again
+      }
       if (p.chan_stats && stat_slot >= 0) {
         // GroupNorm statistics for the consumer of this tensor (mdx_groupnorm_pre): reduce the 8 lanes that hold
         // the same 4 columns (lane = 4*row_lane + q4); lanes 0..3 store the warp's partial sums into its own slot —
         // no atomics, every slot is written exactly once, the consumer adds the slots in a fixed order
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int kk = 0; kk < 4; ++kk) {
 #pragma unroll
           for (int m = 4; m < 32; m <<= 1) {
-            cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], m);
-            cq[k] += __shfl_xor_sync(0xffffffffu, cq[k], m);
+            cs[kk] += __shfl_xor_sync(0xffffffffu, cs[kk], m);
+            cq[kk] += __shfl_xor_sync(0xffffffffu, cq[kk], m);
           }
         }
         if (lane < 4 && col_ok) {
@@ -240,10 +251,6 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
           *reinterpret_cast<float4*>(dst) = make_float4(cs[0], cs[1], cs[2], cs[3]);
           *reinterpret_cast<float4*>(dst + p.N) = make_float4(cq[0], cq[1], cq[2], cq[3]);
         }
-      }
-      if constexpr (HAS_ADD) {
-#pragma unroll
-        for (int pass = 0; pass < 4; ++pass) { radd[pass] = rnext[pass]; rnext[pass] = rnext2[pass]; }
       }
     }
   }
@@ -600,24 +607,15 @@ void pick_tile(int W, int H, int n, int* tw_, int* th_, int* tn_) {
   *tw_ = btw; *th_ = bth; *tn_ = btn;
 }
 
-int num_sms() {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-      sms = 148;
-  }
-  return sms;
-}
+int num_sms() { return mdx_num_sms(); }
 
 template <int BN>
 int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static MdxPerDeviceOnce attr;
+  if (attr.need()) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         TcCfg<BN>::SMEM_BYTES));
-    attr_set = true;
+    attr.mark();
   }
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   TcParams q = p;

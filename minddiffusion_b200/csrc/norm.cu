@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(512) gn_stats_kernel(const GnP p) {
     atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (&bins[0][0])[i]);
 }
 
-template <typename T, typename TO>
+template <typename T, typename TO, bool SILU>
 __global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
   constexpr int V = 8;
   const int cv = threadIdx.x % p.CV, rl = threadIdx.x / p.CV;
@@ -198,7 +198,9 @@ __global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
 #pragma unroll
     for (int i = 0; i < V; ++i) {
       const float y = fmaf(v[i], a[i], b[i]);
-      v[i] = p.silu ? silu_f(y) : y;
+      if constexpr (!SILU) v[i] = y;
+      else if constexpr (sizeof(TO) == 2) v[i] = silu_fast(y);   // bf16 operand of the next GEMM
+      else v[i] = silu_f(y);                                     // fp32 check mode
     }
     Vec<TO>::store(obase + (long long)row * p.ldo, v);
   };
@@ -347,9 +349,10 @@ int launch_gn(GnP p, cudaStream_t st) {
   MDX_CHECK_ARG(p.CV <= 512, "mdx_groupnorm: too many channels (%d)", C);
   p.RP = 512 / p.CV;
   if (p.RP > 16) p.RP = 16;
-  // about two waves of blocks, each at least 8*RP rows (4-deep unrolled loads twice)
+  // about eight waves of blocks (4 resident per SM), so the last, partly filled wave costs a few per cent instead of
+  // a third; each block walks at least 8*RP rows (4-deep unrolled loads twice)
   int chunks = (p.HW + 8 * p.RP - 1) / (8 * p.RP);
-  int want = (8 * 148 + p.n - 1) / p.n;
+  int want = (32 * mdx_num_sms() + p.n - 1) / p.n;
   if (chunks > want) chunks = want;
   if (chunks < 1) chunks = 1;
   p.rows_per_block = (p.HW + chunks - 1) / chunks;
@@ -362,7 +365,8 @@ int launch_gn(GnP p, cudaStream_t st) {
     gn_stats_kernel<T><<<grid, block, 0, st>>>(p);
   }
   MDX_CHECK_LAUNCH();
-  gn_apply_kernel<T, TO><<<grid, block, 0, st>>>(p);
+  if (p.silu) gn_apply_kernel<T, TO, true><<<grid, block, 0, st>>>(p);
+  else gn_apply_kernel<T, TO, false><<<grid, block, 0, st>>>(p);
   MDX_CHECK_LAUNCH();
   g_mdx_launches.fetch_add(2, std::memory_order_relaxed);
   return MDX_OK;

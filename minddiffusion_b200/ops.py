@@ -9,7 +9,7 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import ConvArgs, GemmArgs, check
+from ._lib import STEP_COEFS, ConvArgs, GemmArgs, StepArgs, check
 
 F32, BF16 = 0, 1
 # bench.py sets this to a list to time every mdx_gemm_tc launch with CUDA events: entries (flops, start, end)
@@ -409,6 +409,86 @@ def sampler_dpmpp2m_step(eps_model, x, coef, cfg, scale, C, model_type=0, x0_pre
                                        ctypes.cast(_host_floats(coef), ctypes.c_void_p), _p(x_next), _p(x0_cur), B, C,
                                        h, wd, _stream()), "mdx_sampler_dpmpp2m_step")
     return x_next, x0_cur
+
+
+def plms_coef_row(w, coef, v=None, use_noise=False):
+    """One table row of the PLMS / DDIM step kernel (mdx_sampler_plms_coef_row): w = AB weights (4), coef =
+    (a_t, a_prev, sigma_t, sqrt_one_minus_a_t), v = (v_a, v_s) for a v-prediction model.  Returns a list of floats."""
+    lib = _lib.load()
+    row = (ctypes.c_float * STEP_COEFS)()
+    check(lib.mdx_sampler_plms_coef_row(ctypes.cast(_host_floats(w), ctypes.c_void_p),
+                                        ctypes.cast(_host_floats(coef), ctypes.c_void_p),
+                                        ctypes.cast(_host_floats(v), ctypes.c_void_p) if v is not None else None,
+                                        int(use_noise), ctypes.cast(row, ctypes.c_void_p)),
+          "mdx_sampler_plms_coef_row")
+    return list(row)
+
+
+def sampler_step_ex(kind, model_out, x, x_out, C, cfg, scale, table=None, counter=None, row=None, model_type=0,
+                    x_model=None, hist=(None, None, None), noise=None, pred_x0=None, e_t_out=None, shift_hist=False):
+    """Struct form of the step kernels (mdx_sampler_plms_step_ex / mdx_sampler_dpmpp2m_step_ex).  kind: "plms" or
+    "dpm".  Per-step scalars: `row` (host list of STEP_COEFS floats) or (`table` fp32 [rows, STEP_COEFS], `counter`
+    int32 [1]) on the device."""
+    lib = _lib.load()
+    B, Cx, h, wd = x.shape
+    if Cx != C:
+        raise ValueError("channel mismatch")
+    if not model_out.is_contiguous() or model_out.shape[0] != (2 * B if cfg else B):
+        raise ValueError("model_out must be contiguous NHWC with %d images" % (2 * B if cfg else B))
+    a = StepArgs()
+    a.model_out, a.ld_out, a.model_dtype = model_out.data_ptr(), model_out.shape[-1], _dt(model_out)
+    a.cfg, a.scale, a.model_type = int(cfg), float(scale), int(model_type)
+    f = lambda t, nm: _f32(t, nm).data_ptr() if t is not None else None
+    a.x, a.x_model = f(x, "x"), f(x_model, "x_model")
+    for i in range(3):
+        a.hist[i] = f(hist[i], "hist")
+    a.noise, a.x_out, a.pred_x0, a.e_t_out = f(noise, "noise"), f(x_out, "x_out"), f(pred_x0, "pred_x0"), f(e_t_out, "e_t_out")
+    a.shift_hist = int(shift_hist)
+    a.B, a.C, a.h, a.w = B, C, h, wd
+    keep = None
+    if row is not None:
+        if len(row) != STEP_COEFS:
+            raise ValueError("row must hold %d floats" % STEP_COEFS)
+        keep = _host_floats(row)
+        a.coef_host = ctypes.cast(keep, ctypes.c_void_p)
+    else:
+        if table.dtype != torch.float32 or not table.is_contiguous() or table.shape[-1] != STEP_COEFS:
+            raise ValueError("table must be contiguous float32 [rows, %d]" % STEP_COEFS)
+        if counter.dtype != torch.int32 or not counter.is_cuda:
+            raise ValueError("counter must be an int32 CUDA tensor")
+        a.coef_table, a.step_dev = table.data_ptr(), counter.data_ptr()
+    fn = lib.mdx_sampler_plms_step_ex if kind == "plms" else lib.mdx_sampler_dpmpp2m_step_ex
+    check(fn(ctypes.byref(a), _stream()), "mdx_sampler_%s_step_ex" % kind)
+    return x_out
+
+
+def step_advance(counter, delta=1):
+    check(_lib.load().mdx_step_advance(_p(counter), int(delta), _stream()), "mdx_step_advance")
+
+
+def gather_row(table, counter, out, offset=0):
+    """out[j, :] = table[counter + offset, :] for every row j of out (a 1-D out is n rows of width 1)."""
+    t2 = table if table.dim() == 2 else table.view(-1, 1)
+    o2 = out if out.dim() == 2 else out.view(-1, 1)
+    if t2.dtype != torch.float32 or o2.dtype != torch.float32 or not o2.is_contiguous() or t2.stride(-1) != 1:
+        raise TypeError("gather_row takes float32 tensors")
+    check(_lib.load().mdx_gather_row(_p(t2), t2.stride(0), _p(counter), int(offset), _p(o2), o2.shape[0], o2.shape[1],
+                                     _stream()), "mdx_gather_row")
+    return out
+
+
+def sampler_mask_blend(img, x0, noise, mask, sqrt_ac, sqrt_1m_ac):
+    """img <- q_sample(x0, t, noise) * mask + (1 - mask) * img in place (plms.py:153-156); fp32 NCHW, mask [B, 1 or C, h, w]."""
+    B, C, h, w = img.shape
+    mask = _f32(mask, "mask")
+    if mask.dim() != 4 or mask.shape[0] != B or mask.shape[2:] != img.shape[2:] or mask.shape[1] not in (1, C):
+        raise ValueError("mask must be [B, 1 or C, h, w]")
+    if x0.shape != img.shape or noise.shape != img.shape:
+        raise ValueError("x0 / noise must have the latent's shape")
+    check(_lib.load().mdx_sampler_mask_blend(_p(_f32(x0, "x0")), _p(_f32(noise, "noise")), _p(mask), mask.shape[1],
+                                             float(sqrt_ac), float(sqrt_1m_ac), _p(_f32(img, "img")), B, C, h, w,
+                                             _stream()), "mdx_sampler_mask_blend")
+    return img
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -47,24 +47,36 @@ class CfgPairSplit:
             raise ValueError("CFG pair split needs an even number of ranks (got %d)" % self.world)
         self.pair = self.rank // 2
         self.is_cond = self.rank % 2 == 1
-        self.group = None
-        # every rank must create every group, in the same order
-        for p in range(self.world // 2):
-            g = dist.new_group(ranks=[2 * p, 2 * p + 1])
-            if p == self.pair:
-                self.group = g
+        if self.world == 2:
+            self.group = dist.group.WORLD
+        else:  # new_group is collective over the default group: every rank creates every pair's group, in order
+            self.group = None
+            for p in range(self.world // 2):
+                g = dist.new_group(ranks=[2 * p, 2 * p + 1])
+                if p == self.pair:
+                    self.group = g
         self.n_pairs = self.world // 2
 
     def my_context(self, cond, uncond):
         return cond if self.is_cond else uncond
 
-    def exchange(self, eps_local, out=None):
+    def exchange(self, eps_local, out=None, channels=None):
         """eps_local: this rank's UNet output [B, ...].  Returns [2B, ...] with the unconditional half first — the
-        row order the fused combine+update kernel expects (the concat order of plms.py:192-194)."""
+        row order the fused combine+update kernel expects (the concat order of plms.py:192-194).
+
+        channels: only the first `channels` entries of the last dim carry data (the tensor-core conv_out pads its 4
+        output channels to 16 columns): they are packed into [B, ..., channels] with one strided row copy before the
+        exchange, so 1/4 of the bytes cross NVLink.  One NCCL all-gather into a contiguous tensor — capturable in a
+        CUDA graph, which is how the step plans of samplers.py issue it."""
         eps_local = eps_local.contiguous()
-        if out is None:
-            out = torch.empty((2 * eps_local.shape[0],) + tuple(eps_local.shape[1:]), dtype=eps_local.dtype,
-                              device=eps_local.device)
+        ld = eps_local.shape[-1]
+        if channels is not None and channels != ld and eps_local.is_cuda and (channels * eps_local.element_size()) % 16 == 0:
+            from . import ops
+            packed = torch.empty(tuple(eps_local.shape[:-1]) + (channels,), dtype=eps_local.dtype, device=eps_local.device)
+            ops.copy_rows(eps_local.view(1, -1, ld)[:, :, :channels], packed.view(1, -1, channels))
+            eps_local = packed
         B = eps_local.shape[0]
-        dist.all_gather([out[:B], out[B:]], eps_local, group=self.group)
+        if out is None:
+            out = torch.empty((2 * B,) + tuple(eps_local.shape[1:]), dtype=eps_local.dtype, device=eps_local.device)
+        dist.all_gather_into_tensor(out, eps_local, group=self.group)
         return out

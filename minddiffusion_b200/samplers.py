@@ -17,7 +17,7 @@ materialised: the UNet reads the latent batch twice.
 import numpy as np
 import torch
 
-from . import ops
+from . import _lib, ops
 
 
 def make_ddim_timesteps(ddim_discr_method="uniform", num_ddim_timesteps=50, num_ddpm_timesteps=1000, verbose=False):
@@ -45,8 +45,9 @@ def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta=0.0, verbose=Fa
 
 
 def _check_unsupported(mask, x0, score_corrector, quantize_x0, noise_dropout):
-    if mask is not None or x0 is not None:
-        raise NotImplementedError("mask/x0 (inpainting blend, plms.py:156-159) is outside this path's scope")
+    if mask is not None and x0 is None:
+        raise AssertionError("x0 must be given with mask")  # plms.py:154 `assert x0 is not None`
+    # x0 without a mask is ignored, as the reference does (plms.py:153; inpaint.py:95-106 calls it that way)
     if score_corrector is not None:
         raise NotImplementedError("score_corrector is not supported")
     if quantize_x0:
@@ -55,21 +56,127 @@ def _check_unsupported(mask, x0, score_corrector, quantize_x0, noise_dropout):
         raise NotImplementedError("noise_dropout is not supported")
 
 
+def _model_type(model):
+    """0: the network predicts eps; 1: it predicts v and the step kernel converts (dpm_solver.py:281-284).  The
+    reference's PLMS assumes eps (plms.py:200); "x0" networks are not used by any shipped config."""
+    par = getattr(model, "parameterization", "eps")
+    if par == "eps":
+        return 0
+    if par == "v":
+        return 1
+    raise NotImplementedError('parameterization "%s" is not supported by the sampler kernels' % par)
+
+
 def _warn_batch(conditioning, batch_size):
     if conditioning is not None:  # plms.py:93-100
         if isinstance(conditioning, dict):
-            cbs = conditioning[list(conditioning.keys())[0]].shape[0]
+            cbs = conditioning[list(conditioning.keys())[0]]
+            cbs = (cbs[0] if isinstance(cbs, (list, tuple)) else cbs).shape[0]
         else:
             cbs = conditioning.shape[0]
         if cbs != batch_size:
             print("Warning: Got %d conditionings but batch-size is %d" % (cbs, batch_size))
 
 
+MAX_ROWS = 1002   # table rows of a step plan: one per UNet evaluation of a loop (S <= 1000, + the pseudo-Euler extra)
+
+
+class _StepPlan:
+    """State and launch sequences of one sampler loop on one latent shape.
+
+    A step is: timestep row -> UNet evaluation (the guided batch reads the latent twice) -> ONE combine + update
+    kernel -> counter advance.  Every per-step scalar lives in device tables (`table`: kernel coefficients, `t_table`:
+    model-input times) indexed by the device `counter`, and every tensor the step touches has a fixed address, so
+    the launches of a step are the same from step to step: with `unet.use_cuda_graph` each phase is captured once and
+    the host loop only replays it; without, the same functions run eagerly.
+
+    Phases: "first" (PLMS pseudo improved Euler, plms.py:231-235: two evaluations), "multi" (PLMS Adams-Bashforth
+    2/3/4 — the weights are table entries, the eps history shifts inside the kernel), "ddim", "dpm".
+    """
+
+    def __init__(self, unet, B, C, H, W, cfg, scale, model_type, split):
+        dev = unet.device
+        z = lambda: torch.zeros((B, C, H, W), dtype=torch.float32, device=dev)
+        self.unet, self.C, self.cfg, self.scale, self.model_type, self.split = unet, C, cfg, float(scale), model_type, split
+        self.img, self.x_tmp, self.pred_x0, self.noise = z(), z(), z(), z()
+        self.hist = [z(), z(), z()]
+        self.table = torch.zeros((MAX_ROWS, ops.STEP_COEFS), dtype=torch.float32, device=dev)
+        self.t_table = torch.zeros((MAX_ROWS,), dtype=torch.float32, device=dev)
+        self.counter = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.repeat = 2 if (cfg and split is None) else 1
+        self.t = torch.zeros(B * self.repeat, dtype=torch.float32, device=dev)
+        self.graphs = {}
+        if unet._ctx is None or unet._ctx["n"] != B * self.repeat:
+            raise ValueError("context batch does not match the latent batch")
+
+    def load_tables(self, rows, times):
+        if len(rows) > MAX_ROWS:
+            raise ValueError("too many steps for a step plan")
+        self.table[:len(rows)].copy_(torch.tensor(rows, dtype=torch.float32))
+        self.t_table[:len(times)].copy_(torch.tensor(times, dtype=torch.float32))
+        self.counter.zero_()
+        for h in self.hist:
+            h.zero_()
+
+    # ---- launch sequences (identical eager and under capture) ----
+    def _eval(self, x):
+        ops.gather_row(self.t_table, self.counter, self.t)
+        out = self.unet._forward_impl(x, self.t, self.repeat, None, True)
+        if self.split is not None:
+            out = self.split.exchange(out, channels=self.C)
+        return out
+
+    def _kernel(self, kind, out, **kw):
+        ops.sampler_step_ex(kind, out, self.img, kw.pop("x_out", self.img), self.C, self.cfg, self.scale,
+                            table=self.table, counter=self.counter, model_type=self.model_type, **kw)
+        ops.step_advance(self.counter, 1)
+
+    def _run_first(self):
+        out = self._eval(self.img)
+        self._kernel("plms", out, x_out=self.x_tmp, e_t_out=self.hist[0])
+        out = self._eval(self.x_tmp)
+        self._kernel("plms", out, x_model=self.x_tmp, hist=(self.hist[0], None, None), pred_x0=self.pred_x0)
+
+    def _run_multi(self):
+        self._kernel("plms", self._eval(self.img), hist=tuple(self.hist), shift_hist=True, pred_x0=self.pred_x0)
+
+    def _run_ddim(self):
+        self._kernel("plms", self._eval(self.img), noise=self.noise, pred_x0=self.pred_x0)
+
+    def _run_dpm(self):
+        self._kernel("dpm", self._eval(self.img), hist=(self.hist[0], None, None), pred_x0=self.hist[0])
+
+    def run(self, phase):
+        fn = getattr(self, "_run_" + phase)
+        if not self.unet.use_cuda_graph:
+            fn()
+            return
+        ent = self.graphs.get(phase)
+        if ent is None:
+            # warm-up (kernel attributes, allocator) on a snapshot of the loop state, then capture; capture itself
+            # executes nothing
+            state = [self.img, self.x_tmp, self.pred_x0, self.counter] + self.hist
+            saved = [t.clone() for t in state]
+            fn()
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
+            with torch.cuda.graph(graph, pool=self.unet.graph_pool()):
+                fn()
+            ent = (graph, _lib.launch_count() - n0)
+            self.graphs[phase] = ent
+            for t, sv in zip(state, saved):
+                t.copy_(sv)
+        ent[0].replay()
+        self.unet.replayed_launches += ent[1]
+
+
 class _GuidedUNet:
-    """Binds (cond, uncond, scale) to the UNet: evaluates the (2B when guided) batch and tells the step kernel
-    whether to combine."""
+    """Binds (cond, uncond, scale) to the UNet — hoisted cross-attention K/V, concat conditioning, the optional CFG
+    pair split — and hands out the step plan for a latent shape."""
 
     def __init__(self, model, cond, uncond, scale):
+        self.model = model
         self.unet = model.unet
         self.cfg = not (uncond is None or scale == 1.0)  # plms.py:189
         self.scale = float(scale)
@@ -95,13 +202,13 @@ class _GuidedUNet:
         else:
             self.unet.set_concat(torch.cat((uc_cat, c_cat), dim=0) if self.cfg else c_cat)
 
-    def __call__(self, x, t_value):
-        if self.split is not None:
-            t = torch.full((x.shape[0],), float(t_value), dtype=torch.float32, device=x.device)
-            return self.split.exchange(self.unet.forward_nhwc(x, t, repeat=1, uniform_t=True))  # [uncond | cond]
-        n = x.shape[0] * (2 if self.cfg else 1)
-        t = torch.full((n,), float(t_value), dtype=torch.float32, device=x.device)
-        return self.unet.forward_nhwc(x, t, repeat=2 if self.cfg else 1, uniform_t=True)
+    def plan(self, shape):
+        B, C, H, W = shape
+        key = ("step", B, C, H, W, self.cfg, self.scale, _model_type(self.model), self.split is not None)
+        plans = self.unet._graphs   # dropped together with the UNet's own graphs when a captured buffer moves
+        if key not in plans:
+            plans[key] = _StepPlan(self.unet, B, C, H, W, self.cfg, self.scale, _model_type(self.model), self.split)
+        return plans[key]
 
 
 class PLMSSampler(object):
@@ -152,6 +259,35 @@ class PLMSSampler(object):
                                   unconditional_guidance_scale=unconditional_guidance_scale,
                                   unconditional_conditioning=unconditional_conditioning, verbose=verbose)
 
+    def _tables(self, time_range, model_type):
+        """One (coefficient row, model-input time) per UNet evaluation, in launch order."""
+        total = len(time_range)
+        ac = self.alphas_cumprod
+        rows, times = [], []
+
+        def v_of(step):   # v -> eps at the evaluated timestep: eps = sqrt(abar_t) v + sqrt(1 - abar_t) x
+            return (np.sqrt(ac[step]), np.sqrt(np.float32(1.) - ac[step])) if model_type == 1 else None
+
+        for i, step in enumerate(time_range):
+            index = total - i - 1
+            step_next = time_range[min(i + 1, total - 1)]
+            coef = (self.ddim_alphas[index], self.ddim_alphas_prev[index], self.ddim_sigmas[index],
+                    self.ddim_sqrt_one_minus_alphas[index])
+            if self.ddim:
+                w = [((1., 0., 0., 0.), step)]
+            elif i == 0:   # pseudo improved Euler, plms.py:231-235
+                w = [((1., 0., 0., 0.), step), ((.5, .5, 0., 0.), step_next)]
+            elif i == 1:   # Adams-Bashforth 2 / 3 / 4, plms.py:236-244
+                w = [((3 / 2, -1 / 2, 0., 0.), step)]
+            elif i == 2:
+                w = [((23 / 12, -16 / 12, 5 / 12, 0.), step)]
+            else:
+                w = [((55 / 24, -59 / 24, 37 / 24, -9 / 24), step)]
+            for wk, st in w:
+                rows.append(ops.plms_coef_row(wk, coef, v_of(int(st)), use_noise=self.ddim))
+                times.append(float(int(st)))
+        return rows, times
+
     def plms_sampling(self, cond, shape, x_T=None, ddim_use_original_steps=False, callback=None, timesteps=None,
                       quantize_denoised=False, mask=None, x0=None, img_callback=None, log_every_t=100,
                       temperature=1., noise_dropout=0., score_corrector=None, corrector_kwargs=None,
@@ -160,57 +296,40 @@ class PLMSSampler(object):
         if ddim_use_original_steps or timesteps is not None:
             raise NotImplementedError("ddim_use_original_steps / explicit timesteps are not used by txt2img")
         device = self.model.unet.device
-        b, C = shape[0], shape[1]
-        img = torch.randn(shape, device=device, dtype=torch.float32) if x_T is None else \
-            x_T.to(device=device, dtype=torch.float32).contiguous().clone()
         unet = _GuidedUNet(self.model, cond, unconditional_conditioning, unconditional_guidance_scale)
+        plan = unet.plan(shape)
+        plan.img.copy_(torch.randn(shape, device=device, dtype=torch.float32) if x_T is None else
+                       x_T.to(device=device, dtype=torch.float32))
         time_range = np.flip(self.ddim_timesteps)
         total_steps = self.ddim_timesteps.shape[0]
+        plan.load_tables(*self._tables(time_range, plan.model_type))
+        if mask is not None:
+            mask = mask.to(device=device, dtype=torch.float32).contiguous()
+            x0 = x0.to(device=device, dtype=torch.float32).contiguous()
         if verbose:
             print("Running %s Sampling with %d timesteps" % ("DDIM" if self.ddim else "PLMS", total_steps))
-        intermediates = {'x_inter': [img], 'pred_x0': [img]}
-        old_eps = []
+        first = plan.img.clone()
+        intermediates = {'x_inter': [first], 'pred_x0': [first]}
         for i, step in enumerate(time_range):
             index = total_steps - i - 1
-            step_next = time_range[min(i + 1, len(time_range) - 1)]
-            coef = (self.ddim_alphas[index], self.ddim_alphas_prev[index], self.ddim_sigmas[index],
-                    self.ddim_sqrt_one_minus_alphas[index])
-            noise = None
-            if float(self.ddim_sigmas[index]) != 0.0:  # noise_like(...) * temperature, plms.py:222
-                noise = torch.randn(shape, device=device, dtype=torch.float32) * temperature
-            eps_m = unet(img, int(step))
-            e_t = torch.empty_like(img)
-            pred_x0 = torch.empty_like(img)
+            if mask is not None:  # plms.py:153-156: img = q_sample(x0, ts, randn) * mask + (1 - mask) * img
+                ops.sampler_mask_blend(plan.img, x0, torch.randn(shape, device=device, dtype=torch.float32), mask,
+                                       self.model.sqrt_alphas_cumprod[step],
+                                       self.model.sqrt_one_minus_alphas_cumprod[step])  # model.q_sample, ddpm.py:180-182
             if self.ddim:
-                img = ops.sampler_plms_step(eps_m, img, (1., 0., 0., 0.), coef, unet.cfg, unet.scale, C, noise=noise,
-                                            pred_x0=pred_x0, e_t_out=e_t)
-            elif len(old_eps) == 0:
-                # Pseudo Improved Euler (2nd order), plms.py:231-235: a second UNet evaluation at (x_prev, t_next)
-                x_tmp = ops.sampler_plms_step(eps_m, img, (1., 0., 0., 0.), coef, unet.cfg, unet.scale, C,
-                                              noise=noise, e_t_out=e_t)
-                eps_next = unet(x_tmp, int(step_next))
-                img = ops.sampler_plms_step(eps_next, img, (.5, .5, 0., 0.), coef, unet.cfg, unet.scale, C,
-                                            old=(e_t, None, None), noise=noise, pred_x0=pred_x0)
+                if float(self.ddim_sigmas[index]) != 0.0:  # noise_like(...) * temperature, plms.py:222
+                    plan.noise.normal_().mul_(temperature)
+                plan.run("ddim")
             else:
-                if len(old_eps) == 1:  # Adams-Bashforth 2 / 3 / 4, plms.py:236-244
-                    w, old = (3 / 2, -1 / 2, 0., 0.), (old_eps[-1], None, None)
-                elif len(old_eps) == 2:
-                    w, old = (23 / 12, -16 / 12, 5 / 12, 0.), (old_eps[-1], old_eps[-2], None)
-                else:
-                    w, old = (55 / 24, -59 / 24, 37 / 24, -9 / 24), (old_eps[-1], old_eps[-2], old_eps[-3])
-                img = ops.sampler_plms_step(eps_m, img, w, coef, unet.cfg, unet.scale, C, old=old, noise=noise,
-                                            pred_x0=pred_x0, e_t_out=e_t)
-            old_eps.append(e_t)
-            if len(old_eps) >= 4:
-                old_eps.pop(0)
+                plan.run("first" if i == 0 else "multi")
             if callback:
                 callback(i)
             if img_callback:
-                img_callback(pred_x0, i)
+                img_callback(plan.pred_x0, i)
             if index % log_every_t == 0 or index == total_steps - 1:
-                intermediates['x_inter'].append(img)
-                intermediates['pred_x0'].append(pred_x0)
-        return img, intermediates
+                intermediates['x_inter'].append(plan.img.clone())
+                intermediates['pred_x0'].append(plan.pred_x0.clone())
+        return plan.img.clone(), intermediates
 
 
 class DDIMSampler(PLMSSampler):
@@ -283,20 +402,20 @@ class DPMSolverSampler(object):
         size = (batch_size, C, H, W)
         device = self.model.unet.device
         img = torch.randn(size, device=device, dtype=torch.float32) if x_T is None else \
-            x_T.to(device=device, dtype=torch.float32).contiguous().clone()
+            x_T.to(device=device, dtype=torch.float32)
         ns = NoiseScheduleVP('discrete', alphas_cumprod=self.alphas_cumprod)
         # sampler.py:77-85 hard-codes model_type="noise"; "v" (dpm_solver.py:281-284) is selected by the model's
         # parameterization so that the 768-v configuration runs through the same wrapper arithmetic.
-        model_type = 1 if getattr(self.model, "parameterization", "eps") == "v" else 0
         unet = _GuidedUNet(self.model, conditioning, unconditional_conditioning, unconditional_guidance_scale)
+        plan = unet.plan(size)
         order, steps = 2, S
         if steps < order:
             raise AssertionError("steps >= order")  # dpm_solver.py:1064
         t_0, t_T = 1. / ns.total_N, ns.T
         # get_time_steps('time_uniform'): fp32 linspace cast to fp16 (dpm_solver.py:414-415)
         timesteps = np.linspace(np.float32(t_T), np.float32(t_0), steps + 1, dtype=np.float32).astype(np.float16)
-        x = img.to(torch.float16).to(torch.float32)  # ops.Cast()(img, ms.float16), sampler.py:89
-        x0_prev = None
+        plan.img.copy_(img.to(torch.float16).to(torch.float32))  # ops.Cast()(img, ms.float16), sampler.py:89
+        rows, times = [], []
         for i in range(steps):
             s16 = timesteps[i]
             # get_model_input_time on the fp16 tensor: (t - 1/N) * 1000 (dpm_solver.py:256-265)
@@ -315,21 +434,21 @@ class DPMSolverSampler(object):
                 step_order = min(order, steps + 1 - step)
             else:
                 step_order = order
-            if step_order == 1 or x0_prev is None:
+            if step_order == 1 or i == 0:
                 # dpm_solver_first_update, predict_x0 branch (dpm_solver.py:504-513)
-                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -alpha_t * np.expm1(-h), 0.)
-                x0p = None
+                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -alpha_t * np.expm1(-h), 0., 0.)
             else:
                 # multistep_dpm_solver_second_update, 'dpm_solver' type (dpm_solver.py:756-777)
                 lam_p1 = ns.marginal_lambda(np.float32(timesteps[i - 1]))[0]
                 h_0 = lam_s - lam_p1
                 r0 = h_0 / h
                 c = alpha_t * (np.exp(-h) - 1.)
-                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -c, -0.5 * c / r0)
-                x0p = x0_prev
-            out = unet(x, float(t_input))
-            x, x0_prev = ops.sampler_dpmpp2m_step(out, x, coef, unet.cfg, unet.scale, C, model_type=model_type,
-                                                  x0_prev=x0p)
+                coef = (alpha_s, sigma_s, sigma_t / sigma_s, -c, -0.5 * c / r0, 1.)
+            rows.append([float(np.float32(v)) for v in coef] + [0.] * (ops.STEP_COEFS - len(coef)))
+            times.append(float(t_input))
+        plan.load_tables(rows, times)
+        for i in range(steps):
+            plan.run("dpm")
             if callback:
                 callback(i)
-        return x, None
+        return plan.img.clone(), None

@@ -120,15 +120,23 @@ class TextEncoder:
 
 
 class FrozenCLIPEmbedder_ZH:
-    """encoders/modules.py:23-41 minus the tokenizer: `encode(token_ids)` / `__call__(token_ids)`."""
+    """encoders/modules.py:23-41: `encode(token ids [B, 77])` / `__call__(token ids)`; `tokenize(texts)` is the family's
+    tokenizer (minddiffusion_b200.tokenizer) and `encode(list of str)` goes through it."""
 
     def __init__(self, params, dtype=torch.bfloat16, device="cuda", **cfg):
         self.transformer = TextEncoder(params, dtype=dtype, device=device, **(cfg or SD2_TEXT))
         self.max_length = self.transformer.cfg["context_length"]
 
+    def tokenize(self, texts):
+        from . import tokenizer
+        if self.transformer.cfg.get("quick_gelu", False):      # wukong-huahua tower: WordPiece, [CLS] ... [SEP]
+            return tokenizer.tokenize_zh(texts)
+        return tokenizer.tokenize(texts, truncate=True)
+
     def encode(self, tokens):
         if isinstance(tokens, (str, list)) and (isinstance(tokens, str) or (tokens and isinstance(tokens[0], str))):
-            raise NotImplementedError("tokenisation is outside this path's scope; pass token ids [B, 77]")
+            import torch as _torch
+            tokens = _torch.from_numpy(self.tokenize(tokens))   # FileNotFoundError if the vocabulary file is missing
         return self.transformer(tokens)
 
     __call__ = encode

@@ -9,9 +9,11 @@ Differences that follow from this build's scope:
     same parameter names (`model.diffusion_model...`, `first_stage_model...`, `cond_stage_model...`).  If the file does
     not exist it prints the reference's warning and continues with seeded random weights, as the reference continues
     with its random init (txt2img.py:52-63).
-  * tokenisation (CLIP BPE / WordPiece, `ftfy`, vocabulary files) is host string processing outside the path: prompts
-    are mapped to token ids by `--token_file` (int array [n_prompts, 77]) or, failing that, by a deterministic hash —
-    enough to exercise and time the pipeline, not to draw the prompt.
+  * tokenisation: `minddiffusion_b200.tokenizer` (CLIP BPE for stablediffusionv2, WordPiece for wukong-huahua) with
+    the reference's vocabulary files, which are looked up in $MDX_VOCAB_DIR / <repo>/vocab / a reference checkout;
+    `--token_file` (int array [n_prompts, 77]) supplies ids directly.  Without either the CLI stops with an error;
+    `--hash_prompts` is the explicit opt-in to a deterministic hash of the prompt (pipeline timing only: the images
+    will not depict the prompt, and the CLI says so).
   * --config takes the reference YAML (read with `yaml`; OmegaConf is not needed) or defaults to the shipped values.
 """
 import argparse
@@ -68,6 +70,8 @@ def build_parser():
     p.add_argument("--ddim", action="store_true", help="use the DDIM sampler (eta-parameterised) instead of PLMS")
     p.add_argument("--token_file", type=str, default="", help=".npy int array [n_prompts, 77] of token ids")
     p.add_argument("--family", choices=["sd2", "wukong"], default="sd2", help="used when --config is not readable")
+    p.add_argument("--hash_prompts", action="store_true",
+                   help="no tokenizer vocabulary at hand: stand-in token ids hashed from the prompt (timing runs only)")
     return p
 
 
@@ -118,12 +122,21 @@ def load_model(opt, device="cuda"):
     return model
 
 
-def prompts_to_tokens(prompts, token_table=None, context_length=77, vocab=49408):
+def prompts_to_tokens(prompts, token_table=None, context_length=77, vocab=49408, tokenize_fn=None, hashed=False):
+    """Token ids [n, 77] of the prompts: from `token_table` (prompt -> ids) where it has the prompt, else from
+    `tokenize_fn` (the family's tokenizer, encoders/modules.py:31-36).  hashed=True replaces a missing tokenizer by a
+    deterministic stand-in (well-formed ids that do not encode the prompt)."""
     out = np.zeros((len(prompts), context_length), dtype=np.int64)
     for i, p in enumerate(prompts):
         if token_table is not None and p in token_table:
             out[i] = token_table[p]
             continue
+        if tokenize_fn is not None:
+            out[i] = tokenize_fn([p])[0]
+            continue
+        if not hashed:
+            raise RuntimeError("no token ids for prompt %r: supply the tokenizer vocabulary ($MDX_VOCAB_DIR), a "
+                               "--token_file, or pass --hash_prompts for a timing run" % p)
         h = hashlib.sha256(p.encode("utf-8")).digest()
         rs = np.random.RandomState(int.from_bytes(h[:4], "little"))
         n = min(context_length - 2, max(1, len(p.split())))
@@ -131,6 +144,23 @@ def prompts_to_tokens(prompts, token_table=None, context_length=77, vocab=49408)
         out[i, 1:1 + n] = rs.randint(1, vocab - 2, size=n)
         out[i, 1 + n] = vocab - 1                              # <end_of_text>
     return out
+
+
+def family_tokenizer(cond_stage_model):
+    """The tokenizer FrozenCLIPEmbedder_ZH pairs with its tower: CLIP BPE `tokenize` for stablediffusionv2
+    (encoders/modules.py:28), WordPiece with [CLS]/[SEP] for wukong-huahua (its modules.py:28-50).  None when the
+    vocabulary file cannot be found (the caller then needs --token_file for every prompt)."""
+    from . import tokenizer
+    zh = cond_stage_model.transformer.cfg.get("quick_gelu", False)      # the wukong tower's marker (WUKONG_TEXT)
+    try:
+        if zh:
+            tk = tokenizer.WordpieceTokenizer()
+            return lambda texts: tokenizer.tokenize_zh(texts, tokenizer=tk)
+        tk = tokenizer.SimpleTokenizer()
+        return lambda texts: tokenizer.tokenize(texts, truncate=True, tokenizer=tk)
+    except FileNotFoundError as e:
+        print("tokenizer vocabulary not found (%s)" % e)
+        return None
 
 
 def main(argv=None):
@@ -167,7 +197,11 @@ def main(argv=None):
     start_code = None
     if opt.fixed_code:
         start_code = torch.randn((opt.n_samples, 4, opt.H // 8, opt.W // 8), device=dev)
-    encode = lambda ps: model.get_learned_conditioning(torch.from_numpy(prompts_to_tokens(ps, token_table)).to(dev))
+    tokenize_fn = None if opt.hash_prompts else family_tokenizer(model.cond_stage_model)
+    if opt.hash_prompts:
+        print("!!!Warning!!!: --hash_prompts: token ids are hashed from the prompt text; the images will NOT depict it")
+    encode = lambda ps: model.get_learned_conditioning(torch.from_numpy(
+        prompts_to_tokens(ps, token_table, tokenize_fn=tokenize_fn, hashed=opt.hash_prompts)).to(dev))
     all_samples = []
     for prompts in data:
         for n in range(opt.n_iter):

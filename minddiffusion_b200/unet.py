@@ -365,6 +365,13 @@ class UNetModel:
     # ------------------------------------------------------------------------------------------------
     # public API
     # ------------------------------------------------------------------------------------------------
+    def graph_pool(self):
+        """Memory pool shared by the captured step graphs of samplers.py: they replay one after the other and keep
+        nothing inside the pool between replays, so their temporaries may overlap."""
+        if getattr(self, "_pool", None) is None:
+            self._pool = torch.cuda.graph_pool_handle()
+        return self._pool
+
     def set_concat(self, c_concat):
         """Channel-concatenated conditioning of the 'concat' / 'hybrid' DiffusionWrapper (wukong-huahua ddpm.py:363-372;
         inpainting: mask + masked-image latents, inpaint.py:78-90).  c_concat: [n, Cc, h, w] for the n images of a

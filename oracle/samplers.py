@@ -59,21 +59,32 @@ def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta=0.0):
 # ----------------------------------------------------------------------------------------------------------
 # PLMS / DDIM
 # ----------------------------------------------------------------------------------------------------------
-def _cfg_model_output(model_fn, x, t, c, uc, scale):
-    """get_model_output, plms.py:188-203."""
+def _cfg_model_output(model_fn, x, t, c, uc, scale, v_coef=None):
+    """get_model_output, plms.py:188-203.  v_coef = (sqrt(abar), sqrt(1 - abar)) [1000]: the network predicts v and
+    the guided output is converted with model_wrapper's rule eps = alpha_t * v + sigma_t * x (dpm_solver.py:281-284;
+    the reference's PLMS itself only knows eps networks, plms.py:200)."""
     if uc is None or scale == 1.0:
-        return model_fn(x, t, c)
-    x_in = torch.cat((x, x), dim=0)
-    t_in = torch.cat((t, t), dim=0)
-    c_in = torch.cat((uc, c), dim=0)
-    e_u, e_c = model_fn(x_in, t_in, c_in).chunk(2, dim=0)
-    return e_u + scale * (e_c - e_u)
+        out = model_fn(x, t, c)
+    else:
+        x_in = torch.cat((x, x), dim=0)
+        t_in = torch.cat((t, t), dim=0)
+        c_in = torch.cat((uc, c), dim=0)
+        e_u, e_c = model_fn(x_in, t_in, c_in).chunk(2, dim=0)
+        out = e_u + scale * (e_c - e_u)
+    if v_coef is not None:
+        a = torch.tensor(v_coef[0][int(t[0])], dtype=torch.float32)
+        sg = torch.tensor(v_coef[1][int(t[0])], dtype=torch.float32)
+        out = a * out + sg * x
+    return out
 
 
 def plms_sample(model_fn, sched, S, x_T, cond, uncond=None, scale=1.0, eta=0.0, ddim=False, noise_fn=None,
-                log_every_t=100, record=None):
+                log_every_t=100, record=None, model_type="noise", mask=None, x0=None, blend_noise_fn=None):
     """PLMSSampler.sample -> plms_sampling -> p_sample_plms (plms.py:69-248). With ddim=True every step uses
-    e' = e_t (no multistep), which is the DDIM sampler the metric names.  Returns (img, intermediates)."""
+    e' = e_t (no multistep), which is the DDIM sampler the metric names.  Returns (img, intermediates).
+    mask / x0: the inpainting blend of plms.py:153-156, `img = q_sample(x0, ts, randn) * mask + (1 - mask) * img`
+    (q_sample: wukong-huahua ddpm.py:180-182); blend_noise_fn(shape) supplies the draw.  x0 without a mask is
+    ignored, as in the reference."""
     if eta != 0 and not ddim:
         raise ValueError("ddim_eta must be 0 for PLMS")  # plms.py:35-36
     ac = sched["alphas_cumprod"]
@@ -83,6 +94,7 @@ def plms_sample(model_fn, sched, S, x_T, cond, uncond=None, scale=1.0, eta=0.0, 
     sqrt_1m = np.sqrt(1.0 - alphas)
     img = x_T.clone()
     b = img.shape[0]
+    v_coef = (np.sqrt(ac), np.sqrt(1.0 - ac)) if model_type == "v" else None
     time_range = np.flip(ts)
     total = ts.shape[0]
     inter = {"x_inter": [img], "pred_x0": [img]}
@@ -102,14 +114,20 @@ def plms_sample(model_fn, sched, S, x_T, cond, uncond=None, scale=1.0, eta=0.0, 
         index = total - i - 1
         t = torch.full((b,), int(step), dtype=torch.int64)
         t_next = torch.full((b,), int(time_range[min(i + 1, len(time_range) - 1)]), dtype=torch.int64)
-        e_t = _cfg_model_output(model_fn, img, t, cond, uncond, scale)
+        if mask is not None:
+            assert x0 is not None
+            a_s = torch.tensor(np.sqrt(ac)[int(step)], dtype=torch.float32)
+            s_s = torch.tensor(np.sqrt(1.0 - ac)[int(step)], dtype=torch.float32)
+            img_orig = a_s * x0 + s_s * blend_noise_fn(x0.shape)
+            img = img_orig * mask + (1.0 - mask) * img
+        e_t = _cfg_model_output(model_fn, img, t, cond, uncond, scale, v_coef)
         if record is not None:
             record.append(e_t)
         if ddim:
             e_prime = e_t
         elif len(old_eps) == 0:  # pseudo improved Euler, plms.py:231-235
             x_p, _ = x_prev_and_x0(img, e_t, index)
-            e_next = _cfg_model_output(model_fn, x_p, t_next, cond, uncond, scale)
+            e_next = _cfg_model_output(model_fn, x_p, t_next, cond, uncond, scale, v_coef)
             if record is not None:
                 record.append(e_next)
             e_prime = (e_t + e_next) / 2

@@ -33,3 +33,16 @@ def tiny_cfg():
 @pytest.fixture(scope="session")
 def tiny_v1_cfg():
     return dict(TINY_UNET_V1)
+
+
+def parity_log(name, value, tol):
+    """Append a measured parity number to gpurun_out/parity_errors.jsonl (scratch; summarised under profiles/), so the
+    errors quoted in BASELINE.md are the ones the tests asserted."""
+    import json
+    try:
+        d = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "parity_errors.jsonl"), "a") as f:
+            f.write(json.dumps({"test": name, "value": float(value), "tol": float(tol)}) + "\n")
+    except OSError:
+        pass

@@ -16,7 +16,7 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     lib = _lib.load()
     header = open(os.path.join(ROOT, "include", "mdx.h")).read()
     declared = set(re.findall(r"\b(mdx_[a-z0-9_]+)\s*\(", header))
-    declared -= {"mdx_gemm_args", "mdx_conv_args"}
+    declared -= {"mdx_gemm_args", "mdx_conv_args", "mdx_step_args"}
     assert declared, "no declarations parsed"
     assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
     for name in declared:
@@ -24,6 +24,27 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     assert lib.mdx_version() >= 100
     assert lib.mdx_gemm_tc_pick_block_n(320, 0) == 160
     assert lib.mdx_gemm_tc_pick_block_n(2560, 1) == 160
+
+
+def test_ctypes_structs_match_the_compiled_header():
+    """The argument structs of the binding (and of the stub in INTEGRATION.md) against the sizes the library was
+    compiled with: a struct that is short by one field makes the library read that field from adjacent memory."""
+    from minddiffusion_b200 import _lib
+    lib = _lib.load()
+    assert ctypes.sizeof(_lib.GemmArgs) == lib.mdx_sizeof_gemm_args()
+    assert ctypes.sizeof(_lib.ConvArgs) == lib.mdx_sizeof_conv_args()
+    assert ctypes.sizeof(_lib.StepArgs) == lib.mdx_sizeof_step_args()
+    assert _lib.GemmArgs.chan_stats.offset == lib.mdx_offsetof_gemm_args_chan_stats()
+    assert _lib.GemmArgs._fields_[-1][0] == "chan_stats"
+    # the documented stub declares the same fields in the same order
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    stub = doc[doc.index("class GemmArgs"):doc.index("lib.mdx_gemm_tc.restype")]
+    assert re.findall(r'\("([a-zA-Z_]+)", ctypes', stub) == [f[0] for f in _lib.GemmArgs._fields_]
+    # plms coefficient rows: the host helper reproduces mdx_sampler_plms_step's arithmetic
+    from minddiffusion_b200 import ops
+    row = ops.plms_coef_row((1.5, -0.5, 0.0, 0.0), (0.25, 0.5, 0.0, 0.8660254), v=(0.5, 0.8660254))
+    assert len(row) == _lib.STEP_COEFS and row[4] == 0.5 and abs(row[5] - 0.70710678) < 1e-7
+    assert abs(row[6] - 0.70710678) < 1e-7 and row[9] == 0.5 and row[11] == 0.0
 
 
 def test_abi_reports_errors_without_touching_the_gpu():

@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import ROOT
+from conftest import ROOT, parity_log
 
 BASE = dict(image_size=16, num_channels=64, num_res_blocks=1, channel_mult=(1, 2), attention_resolutions=(1, 2),
             xf_width=128, xf_layers=2, xf_heads=2, n_vocab=1000, timestep_respacing="1,1,1,1,1,2")
@@ -127,11 +127,13 @@ def test_cuda_unets_against_goldens(dtype, tol, tol_loop):
     base = glide.create_model(glide.random_glide_params(ob, 3, seed=0), **ob)
     out = base(T_(G["base_x"]).cuda(), T_(G["base_t"]).cuda(), T_(G["base_tok"]).cuda(), T_(G["base_mask"]).cuda())
     assert tuple(out.shape) == (4, 6, 16, 16) and out.dtype == torch.float32
+    parity_log("glide tiny base %s" % dtype, rel(out, G["base_out"]), tol)
     assert rel(out, G["base_out"]) < tol
     up = glide.create_upsample_model(glide.random_glide_params(ou, 6, seed=1), **ou)
     out = up(T_(G["up_x"]).cuda(), T_(G["up_t"]).cuda(), T_(G["up_low"]).cuda(), T_(G["up_tok"]).cuda(),
              T_(G["up_mask"]).cuda())
     assert tuple(out.shape) == (2, 6, 32, 32)
+    parity_log("glide tiny up %s" % dtype, rel(out, G["up_out"]), tol)
     assert rel(out, G["up_out"]) < tol
 
 
@@ -278,6 +280,7 @@ def test_cuda_glide_shipped_architectures_bf16():
             ref = og.unet_forward(P, opts, x, t, tok, mask, low_res=lr)
             out = glide.create_upsample_model(P, **opts)(x.cuda(), t.cuda(), lr.cuda(), tok.cuda(), mask.cuda())
         assert tuple(out.shape) == tuple(ref.shape)
+        parity_log("glide shipped %d bf16" % size, rel(out, ref), 2e-2)
         assert rel(out, ref) < 2e-2, (size, rel(out, ref))
 
 
@@ -310,6 +313,7 @@ def test_cuda_srgan_against_golden(dtype, tol):
     net = SRGAN(4, random_srgan_params(4, 0), dtype=dtype)
     y = net.sr_handle(T_(G["x"]).cuda())
     assert tuple(y.shape) == (2, 3, 48, 32) and y.dtype == torch.float32
+    parity_log("srgan %s" % dtype, rel(y, G["y"]), tol)
     assert rel(y, G["y"]) < tol
     assert float(y.abs().max()) <= 1.0
 

@@ -23,11 +23,15 @@ def test_argparse_surface_matches_reference_defaults():
 
 def test_prompt_token_stand_in_is_deterministic_and_well_formed():
     from minddiffusion_b200.txt2img import prompts_to_tokens
-    a = prompts_to_tokens(["a cat", "", "a cat"])
+    with pytest.raises(RuntimeError, match="no token ids"):       # never invents ids silently
+        prompts_to_tokens(["a cat"])
+    a = prompts_to_tokens(["a cat", "", "a cat"], hashed=True)
     assert a.shape == (3, 77) and np.array_equal(a[0], a[2]) and not np.array_equal(a[0], a[1])
     assert a.min() >= 0 and a.max() < 49408 and a[0, 0] == 49406 and 49407 in a[0]
     table = {"a cat": np.arange(77)}
     assert np.array_equal(prompts_to_tokens(["a cat"], table)[0], np.arange(77))
+    fn = lambda texts: np.full((len(texts), 77), 7)
+    assert (prompts_to_tokens(["a dog"], table, tokenize_fn=fn) == 7).all()
 
 
 def test_reference_yaml_is_understood(tmp_path):
@@ -58,7 +62,8 @@ def test_reference_yaml_is_understood(tmp_path):
 def test_txt2img_end_to_end_writes_images(tmp_path):
     from minddiffusion_b200.txt2img import main
     out = main(["--prompt", "a small test", "--H", "128", "--W", "128", "--n_samples", "2", "--n_iter", "1",
-                "--ddim_steps", "2", "--scale", "7.5", "--output_path", str(tmp_path), "--config", "/nonexistent.yaml"])
+                "--ddim_steps", "2", "--scale", "7.5", "--output_path", str(tmp_path), "--config", "/nonexistent.yaml",
+                "--hash_prompts"])
     assert len(out) == 1 and out[0].shape == (2, 3, 128, 128)
     assert np.isfinite(out[0]).all() and out[0].min() >= 0.0 and out[0].max() <= 1.0
     files = sorted(os.listdir(os.path.join(str(tmp_path), "samples")))

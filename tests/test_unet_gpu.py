@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import TINY_UNET, TINY_UNET_V1
+from conftest import TINY_UNET, TINY_UNET_V1, parity_log
 
 pytestmark = pytest.mark.gpu
 
@@ -41,10 +41,9 @@ def inputs(cfg, B, hw, L=77, seed=1):
 def test_tiny_unet_eps(cfg, dtype, tol):
     """Per-evaluation eps of the whole UNet (every layer kind) against the oracle.
 
-    bf16: the max-norm error of one evaluation is a noisy statistic — it is the largest of ~150 rounding points'
-    accumulated noise and moves by +-20 % with the weight draw (measured 6.1e-3 .. 9.2e-3 on B200 over seeds and
-    configs, tools/eps_error_survey.py).  The criterion is therefore asserted on the mean over three weight/input
-    draws (<= 1e-2, the north-star bound) with a 1.25x allowance on any single draw."""
+    bf16: the max-norm error of one evaluation moves by +-20 % with the weight draw (measured 6.1e-3 .. 9.2e-3 on
+    B200 over seeds and configs, tools/eps_error_survey.py); the north-star bound 1e-2 is asserted on each of three
+    weight/input draws."""
     from oracle import sd_unet
     errs = []
     for seed in ((0,) if dtype == torch.float32 else (0, 1, 2)):
@@ -59,11 +58,12 @@ def test_tiny_unet_eps(cfg, dtype, tol):
         worst = {k: rel_err(taps[k].permute(0, 3, 1, 2), taps_ref[k]) for k in taps_ref}
         eps = out[..., :cfg["out_channels"]].permute(0, 3, 1, 2)
         e = rel_err(eps, ref)
-        assert e < 1.25 * tol, "seed %d: eps rel err %.3e; per-block %s" % (seed, e, worst)
+        parity_log("tiny unet eps %s %s seed %d" % ("sd2" if cfg is TINY_UNET else "v1", dtype, seed), e, tol)
+        assert e < tol, "seed %d: eps rel err %.3e; per-block %s" % (seed, e, worst)
         errs.append(e)
         if seed == 0:  # reference call signature: NCHW in, NCHW out, context passed per call
             out2 = model(x.cuda(), t.cuda(), context=ctx.cuda())
-            assert rel_err(out2, ref) < 1.25 * tol
+            assert rel_err(out2, ref) < tol
         del model
     assert sum(errs) / len(errs) < tol, errs
 
@@ -80,8 +80,7 @@ def test_tiny_unet_odd_shapes_bf16():
     ref = sd_unet.unet_forward(Pt, TINY_UNET, x, t, ctx)
     model.set_context(ctx.cuda())
     out = model.forward_nhwc(x.cuda(), t.cuda())
-    # single draw of a structure / indexing test: the 1.25x single-draw allowance of test_tiny_unet_eps applies
-    assert rel_err(out[..., :4].permute(0, 3, 1, 2), ref) < 1.25e-2
+    assert rel_err(out[..., :4].permute(0, 3, 1, 2), ref) < 1e-2
 
 
 def test_cfg_repeat_and_cuda_graph_match_eager():
@@ -155,8 +154,11 @@ def test_sampler_api_errors_and_v_prediction():
     x_T, c = inputs(cfg, 1, 16, seed=5)
     with pytest.raises(ValueError, match="ddim_eta must be 0 for PLMS"):
         samplers.PLMSSampler(ldm).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), eta=0.5, verbose=False)
+    with pytest.raises(AssertionError):   # plms.py:154 `assert x0 is not None`
+        samplers.PLMSSampler(ldm).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), mask=x_T, verbose=False)
     with pytest.raises(NotImplementedError):
-        samplers.PLMSSampler(ldm).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), mask=x_T, x0=x_T, verbose=False)
+        samplers.PLMSSampler(_ldm(model, parameterization="x0")).sample(4, 1, (4, 16, 16), c.cuda(), x_T=x_T.cuda(),
+                                                                       verbose=False)
     # unguided path (scale 1): batch is NOT doubled (plms.py:189-190)
     sched = osamp.register_schedule(1000, 0.00085, 0.012)
     fn = _oracle_model_fn(Pt, cfg)
@@ -195,6 +197,7 @@ def test_sd2_config1_two_step_plms_bf16():
     model.set_context(torch.cat((uc, c), 0).cuda())
     out = model.forward_nhwc(x_T.cuda(), torch.full((2,), 501.0).cuda(), repeat=2)[..., :4].permute(0, 3, 1, 2)
     raw_ref = sd_unet.unet_forward(Pt, cfg, torch.cat((x_T, x_T)), torch.full((2,), 501.0), torch.cat((uc, c)))
+    parity_log("config1_sd2_32 eps bf16", rel_err(out, raw_ref), 1e-2)
     assert rel_err(out, raw_ref) <= 1e-2  # the UNet's eps, per evaluation
     e = out[:1] + 7.5 * (out[1:] - out[:1])
     assert cosine(e, rec[0]) >= 0.999  # guided eps: differences between the halves are amplified 7.5x
@@ -215,7 +218,7 @@ def test_cuda_path_against_executed_reference_goldens(family, cfg):
     x = torch.from_numpy(rs.randn(2, 4, 16, 16).astype(np.float32))
     ctx = torch.from_numpy(rs.randn(2, 77, cfg["context_dim"]).astype(np.float32))
     t = torch.tensor([981.0, 21.0])
-    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 1.25e-2)):
+    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 1e-2)):
         model, _ = build(cfg, dtype, seed=0)
         model.set_context(ctx.cuda())
         eps = model.forward_nhwc(x.cuda(), t.cuda())[..., :4].permute(0, 3, 1, 2)
@@ -238,7 +241,7 @@ def test_cuda_path_against_executed_reference_goldens(family, cfg):
         del model
 
 
-@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)], ids=["fp32", "bf16"])
 def test_hybrid_conditioning_inpainting_shape(dtype, tol):
     """wukong-huahua inpainting (`inpaint.py:78-107`): conditioning is a dict {c_concat: mask + masked-image latents
     (5 channels), c_crossattn: text}; DiffusionWrapper 'hybrid' concatenates x and c_concat on channels
@@ -276,35 +279,94 @@ def test_hybrid_conditioning_inpainting_shape(dtype, tol):
         model(x_T.cuda(), t.cuda(), context=c.cuda())                     # 4 channels into a 9-channel UNet
 
 
-def test_sd2_full_size_50_step_ddim_final_latents():
-    """The north star's end criterion at the bench's own shape: SD2 512-base UNet, 64x64 latent, 50-step DDIM,
-    CFG 7.5.  The CPU oracle cannot run 100 full-size evaluations in test time, so the chain is anchored in two links:
-    (1) ONE full-size guided evaluation of the fp32 check mode against the CPU oracle, <= 1e-4 (and the bf16 path on
-    the same inputs, <= 1.25e-2: single-draw allowance of the 1e-2 mean criterion, see test_tiny_unet_eps);
-    (2) all 50 steps, bf16 product path against the fp32 check mode on the GPU: final latents cosine >= 0.999."""
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)], ids=["fp32", "bf16"])
+def test_inpaint_call_and_mask_blend(dtype, tol):
+    """The reference's own inpainting call (wukong-huahua/inpaint.py:95-106): hybrid dict conditioning, positional
+    (S, batch, shape, cond), `x0=c_cat[:, 1:]` and NO mask — the reference ignores x0 then (plms.py:153).  Then the
+    same call with a mask: img = q_sample(x0, ts, randn) * mask + (1 - mask) * img before every step
+    (plms.py:153-156), the draws replayed in the oracle."""
     from minddiffusion_b200 import samplers
-    from minddiffusion_b200.unet import UNetModel
-    from minddiffusion_b200.weights import random_unet_params
+    from oracle import samplers as osamp
     from oracle import sd_unet
-    cfg = sd_unet.SD2_UNET
-    P = random_unet_params(cfg, 0)
-    x_T = torch.from_numpy(np.random.RandomState(42).randn(1, 4, 64, 64).astype(np.float32))
-    c = torch.from_numpy(np.random.RandomState(43).randn(1, 77, 1024).astype(np.float32))
-    uc = torch.from_numpy(np.random.RandomState(44).randn(1, 77, 1024).astype(np.float32))
-    t = torch.full((2,), 981.0)
-    Pt = {k: torch.from_numpy(v) for k, v in P.items()}
-    ref = sd_unet.unet_forward(Pt, cfg, torch.cat((x_T, x_T)), t, torch.cat((uc, c)))
-    out = {}
-    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 1.25e-2)):
-        model = UNetModel(P, dtype=dtype, **cfg)
-        model.set_context(torch.cat((uc, c), 0).cuda())
-        e = model.forward_nhwc(x_T.cuda(), t.cuda(), repeat=2)[..., :4].permute(0, 3, 1, 2)
-        assert rel_err(e, ref) <= tol, (dtype, rel_err(e, ref))
-        model.use_cuda_graph = True
-        out[dtype], _ = samplers.DDIMSampler(_ldm(model)).sample(
-            50, 1, (4, 64, 64), c.cuda(), x_T=x_T.cuda(), verbose=False, unconditional_guidance_scale=7.5,
-            unconditional_conditioning=uc.cuda(), eta=0.0)
-        del model
-        torch.cuda.empty_cache()
-    assert torch.isfinite(out[torch.bfloat16]).all()
-    assert cosine(out[torch.bfloat16], out[torch.float32]) >= 0.999
+    cfg = dict(TINY_UNET_V1, in_channels=9)
+    model, Pt = build(cfg, dtype)
+    rs = np.random.RandomState(6)
+    B, hw, S = 2, 16, 5
+    start_code = torch.from_numpy(rs.randn(B, 4, hw, hw).astype(np.float32))
+    c_cat = torch.from_numpy(rs.randn(B, 5, hw, hw).astype(np.float32))
+    c = torch.from_numpy(rs.randn(B, 77, cfg["context_dim"]).astype(np.float32))
+    uc_cross = torch.from_numpy(rs.randn(B, 77, cfg["context_dim"]).astype(np.float32))
+    sampler = samplers.PLMSSampler(_ldm(model, conditioning_key="hybrid"))
+    cond = {"c_concat": c_cat.cuda(), "c_crossattn": c.cuda()}
+    uc_full = {"c_concat": c_cat.cuda(), "c_crossattn": uc_cross.cuda()}
+    samples_cfg, intermediates = sampler.sample(S, B, [4, hw, hw], cond, verbose=False, eta=0.0,
+                                                unconditional_guidance_scale=5.0, unconditional_conditioning=uc_full,
+                                                x_T=start_code.cuda(), x0=c_cat[:, 1:].cuda())
+    fn = lambda xx, t, cc: sd_unet.unet_forward(Pt, cfg, torch.cat((xx, c_cat.repeat(xx.shape[0] // B, 1, 1, 1)), 1),
+                                                t.to(torch.float32), cc)
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    ref = osamp.plms_sample(fn, sched, S, start_code, c, uc_cross, 5.0, x0=c_cat[:, 1:])[0]
+    assert cosine(samples_cfg, ref) >= 0.999 and rel_err(samples_cfg, ref) < 6 * tol
+    # with a mask (1 = keep the known region): single-channel mask broadcast over the 4 latent channels
+    mask = (torch.from_numpy(rs.rand(B, 1, hw, hw).astype(np.float32)) > 0.5).float()
+    x0 = c_cat[:, 1:].contiguous()
+    torch.manual_seed(11)
+    draws = [torch.randn(B, 4, hw, hw, device="cuda").cpu() for _ in range(S)]
+    it = iter(draws)
+    ref_m = osamp.plms_sample(fn, sched, S, start_code, c, uc_cross, 5.0, mask=mask, x0=x0,
+                              blend_noise_fn=lambda shape: next(it))[0]
+    torch.manual_seed(11)
+    got_m, _ = sampler.sample(S, B, [4, hw, hw], cond, verbose=False, eta=0.0, unconditional_guidance_scale=5.0,
+                              unconditional_conditioning=uc_full, x_T=start_code.cuda(), x0=x0.cuda(), mask=mask.cuda())
+    assert cosine(got_m, ref_m) >= 0.999 and rel_err(got_m, ref_m) < 6 * tol
+    assert rel_err(got_m, ref) > 0.05   # the blend changed the trajectory
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-4), (torch.bfloat16, 1e-2)], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("which", ["plms", "ddim", "dpm"])
+def test_guided_v_prediction_all_samplers(which, dtype, tol):
+    """A v-prediction network under classifier-free guidance through every sampler: the guided output is converted
+    with eps = sqrt(abar_t) v + sqrt(1 - abar_t) x (dpm_solver.py:281-284) inside the step kernel — for PLMS at the
+    timestep and latent of EACH evaluation, including the pseudo improved Euler one at (x_prev, t_next)."""
+    from minddiffusion_b200 import samplers
+    from oracle import samplers as osamp
+    cfg = TINY_UNET
+    model, Pt = build(cfg, dtype)
+    ldm = _ldm(model, parameterization="v")
+    x_T, c = inputs(cfg, 2, 16, seed=42)
+    uc = torch.from_numpy(np.random.RandomState(44).randn(*c.shape).astype(np.float32))
+    sched = osamp.register_schedule(1000, 0.00085, 0.012)
+    fn = _oracle_model_fn(Pt, cfg)
+    kw = dict(x_T=x_T.cuda(), verbose=False, unconditional_guidance_scale=4.0, unconditional_conditioning=uc.cuda())
+    if which == "dpm":
+        ref = osamp.dpmpp2m_sample(fn, sched, 6, x_T, c, uc, 4.0, model_type="v")
+        out, _ = samplers.DPMSolverSampler(ldm).sample(6, 2, (4, 16, 16), c.cuda(), **kw)
+    else:
+        ref = osamp.plms_sample(fn, sched, 6, x_T, c, uc, 4.0, ddim=(which == "ddim"), model_type="v")[0]
+        cls = samplers.DDIMSampler if which == "ddim" else samplers.PLMSSampler
+        out, _ = cls(ldm).sample(6, 2, (4, 16, 16), c.cuda(), **kw)
+    assert cosine(out, ref) >= 0.999
+    assert rel_err(out, ref) < 10 * tol
+
+
+@pytest.mark.parametrize("which", ["plms", "ddim", "dpm"])
+def test_whole_step_graph_replay_matches_eager(which):
+    """use_cuda_graph captures a whole sampler step (timestep row -> UNet -> combine/update kernel -> counter) once
+    per phase and replays it; the per-step scalars come from device tables.  Same result as the eager launches, on
+    repeated calls and after a change of S (new tables, same graphs)."""
+    from minddiffusion_b200 import samplers
+    model, _ = build(TINY_UNET, torch.bfloat16)
+    ldm = _ldm(model)
+    x_T, c = inputs(TINY_UNET, 2, 16, seed=9)
+    uc = (c * 0.3).cuda()
+    cls = {"plms": samplers.PLMSSampler, "ddim": samplers.DDIMSampler, "dpm": samplers.DPMSolverSampler}[which]
+    run = lambda S: cls(ldm).sample(S, 2, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False,
+                                    unconditional_guidance_scale=7.5, unconditional_conditioning=uc)[0]
+    eager6, eager9 = run(6), run(9)
+    model.use_cuda_graph = True
+    n0 = model.replayed_launches
+    g6, g6b, g9 = run(6), run(6), run(9)
+    assert model.replayed_launches > n0
+    # GroupNorm sums of the 8x8 level use fp64 atomics: runs agree to rounding, not bit for bit
+    assert rel_err(g6, eager6) < 2e-3 and rel_err(g6b, eager6) < 2e-3 and rel_err(g9, eager9) < 2e-3
+    assert rel_err(g9, eager6) > 1e-2

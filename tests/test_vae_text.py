@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import ROOT
+from conftest import ROOT, parity_log
 
 TINY_DD = dict(double_z=True, z_channels=4, resolution=32, in_channels=3, out_ch=3, ch=64, ch_mult=[1, 2, 2],
                num_res_blocks=1, attn_resolutions=[], dropout=0.0)
@@ -68,14 +68,29 @@ def test_cuda_vae_and_text_against_goldens(family, dtype, tol_vae, tol_text):
     vae = AutoencoderKL(random_decoder_params(TINY_DD, 0), ddconfig=TINY_DD, dtype=dtype)
     img = vae.decode(_z().cuda())
     assert tuple(img.shape) == (2, 3, 32, 32)
+    parity_log("vae tiny %s %s" % (family, dtype), rel(img, G["vae_image"]), tol_vae)
     assert rel(img, G["vae_image"]) < tol_vae
     tc = TINY_TEXT[family]
     te = FrozenCLIPEmbedder_ZH(random_text_params(tc, 0), dtype=dtype, **tc)
     out = te.encode(torch.from_numpy(G["text_tokens"]).cuda())
     assert tuple(out.shape) == (2, 77, 128) and out.dtype == torch.float32
+    parity_log("text tower tiny %s %s" % (family, dtype), rel(out, G["text_out"]), tol_text)
     assert rel(out, G["text_out"]) < tol_text
-    with pytest.raises(NotImplementedError):
-        te.encode(["a prompt"])
+    # prompts as strings go through the family's tokenizer (here on the small vocabularies committed with the goldens)
+    from minddiffusion_b200 import tokenizer as T
+    gold = os.path.join(ROOT, "tests", "golden")
+    T._default.clear()
+    if family == "sd2":
+        T._default["bpe"] = T.SimpleTokenizer(os.path.join(gold, "mini_bpe.txt.gz"))
+    else:
+        T._default["zh"] = T.WordpieceTokenizer(os.path.join(gold, "mini_vocab_zh.txt"))
+    try:
+        ids = te.tokenize(["a painting of a cat", ""])
+        assert ids.shape == (2, 77) and ids.max() < tc["vocab_size"] and (ids[1, 2:] == 0).all()
+        from_text = te.encode(["a painting of a cat", ""])
+        assert torch.equal(from_text, te.encode(torch.from_numpy(ids).cuda()))
+    finally:
+        T._default.clear()
 
 
 @pytest.mark.gpu
@@ -89,4 +104,5 @@ def test_cuda_vae_decoder_reference_shape_bf16():
     ref = vae_text.vae_decode({k: torch.from_numpy(v) for k, v in P.items()}, SD_DDCONFIG, z)
     img = AutoencoderKL(P, dtype=torch.bfloat16).decode(z.cuda())
     assert tuple(img.shape) == (1, 3, 128, 128)
+    parity_log("vae shipped-shape bf16", rel(img, ref), 2e-2)
     assert rel(img, ref) < 2e-2

@@ -4,8 +4,8 @@
 custom-op body that is given only tensor addresses and a stream, or a thread barred from the allocator — so the
 per-group sums sit in a fixed array inside the library instead of a caller buffer.  The test drives it through
 the C ABI with ctypes and checks it against the regular `mdx_groupnorm` entry point (same kernels, caller-owned
-scratch), twice in a row on different data: the second call would pick up the first call's sums if the shared
-array were not cleared.  It also checks that a problem larger than the built-in array is refused with a clear
+scratch) and against torch's own group_norm + SiLU on the concatenated input, twice in a row on different data: the
+second call would pick up the first call's sums if the shared array were not cleared.  It also checks that a problem larger than the built-in array is refused with a clear
 message rather than overrunning it.  Tolerances are the ones tests/test_ops_gpu.py uses for GroupNorm
 (1e-4 fp32, 2e-2 bf16 of the output's max magnitude).
 """
@@ -61,6 +61,10 @@ def test_noalloc_groupnorm_matches_regular_entry_point_twice(dtype, out_dtype, t
         torch.cuda.synchronize()
         assert torch.isfinite(got.float()).all()
         assert _rel(got, want) < tol, "call %d" % call
+        # independent check: torch's GroupNorm + SiLU over concat(x1, x2) (what both entry points stand for)
+        xin = torch.cat((x1, x2), dim=-1).float().permute(0, 3, 1, 2)
+        ref = torch.nn.functional.silu(torch.nn.functional.group_norm(xin, 32, gamma, beta, 1e-5)).permute(0, 2, 3, 1)
+        assert _rel(got, ref) < tol, "call %d vs torch" % call
 
 
 def test_noalloc_groupnorm_rejects_sizes_beyond_the_builtin_scratch():
