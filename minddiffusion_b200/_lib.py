@@ -144,7 +144,7 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.build()
+    path = os.environ.get("MDX_LIB") or _build.build()   # MDX_LIB: a pre-built variant of the library (A/B runs)
     if not os.path.exists(path):
         raise MdxError("libmdx_b200.so is missing at %s; run `python -m minddiffusion_b200.build`" % path)
     lib = ctypes.CDLL(path)

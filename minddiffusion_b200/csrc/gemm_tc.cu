@@ -157,15 +157,9 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
     }
   } else {
     constexpr int NCH = BN / 16;
-    constexpr int CSTEP = TcCfg<BN>::EPI_WARPS / 4;            // == cstep
-    constexpr int MAXC = (NCH + CSTEP - 1) / CSTEP;            // chunks one warp can own in a tile (<= 6)
-    constexpr int NBUF = MAXC < 4 ? MAXC : 4;
-    // Residual (+ per-image bias) operands: the loads of ALL of this warp's chunks of the tile (up to four; the rest
-    // as buffers free up) are issued before the accumulator is even ready — nothing here depends on the MMAs, and a
-    // whole tile's worth of bytes in flight per SM is what keeps HBM busy.  The chunk loop is fully unrolled so every
-    // buffer is a fixed set of registers: rotating buffers with register moves would make each move wait for the load
-    // it copies, which serialises the loads again.
-    float4 radd[NBUF][4];
+    // residual (+ per-image bias) of this warp's first TWO chunks, requested before the accumulator is even ready:
+    // nothing here depends on the MMAs, and two chunks in flight per warp keep enough bytes outstanding for HBM
+    float4 radd[4], rnext[4];
     auto load_add = [&](float4 (&dst)[4], int c) {
       const int col = ocol_tile + c * 16 + q4 * 4;
       const bool ok = c < NCH && col < n_out;
@@ -177,20 +171,21 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
       }
     };
     if constexpr (HAS_ADD) {
-#pragma unroll
-      for (int k = 0; k < NBUF; ++k) load_add(radd[k], cpar + k * CSTEP);
+      load_add(radd, cpar);
+      load_add(rnext, cpar + cstep);
     }
     mbar_wait(tfull_bar, tfull_parity);
     tc_fence_after();
-#pragma unroll
-    for (int k = 0; k < MAXC; ++k) {
-      const int c = cpar + k * CSTEP;
+#pragma unroll 1
+    for (int c = cpar; c < NCH; c += cstep) {
       const int ocol0 = ocol_tile + c * 16;
-      if (c >= NCH || ocol0 >= n_out) continue;                 // warp-uniform
+      if (ocol0 >= n_out) break;
       const int col = ocol0 + q4 * 4;
       const bool col_ok = col < n_out;
       uint32_t r[16];
       tmem_ld16(taddr + c * 16, r);
+      float4 rnext2[4];
+      if constexpr (HAS_ADD) load_add(rnext2, c + 2 * cstep);   // two chunks ahead
       float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
       if (col_ok && p.bias) bz = __ldg(reinterpret_cast<const float4*>(p.bias + col));
       tmem_ld_wait();
@@ -207,10 +202,7 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
         if (p.act) {  // activation sits between the bias and the residual
           o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act);
         }
-        if constexpr (HAS_ADD) {
-          const float4 a4 = radd[k % NBUF][pass];
-          o.x += a4.x; o.y += a4.y; o.z += a4.z; o.w += a4.w;
-        }
+        if constexpr (HAS_ADD) { o.x += radd[pass].x; o.y += radd[pass].y; o.z += radd[pass].z; o.w += radd[pass].w; }
         const long long pix = pix8[pass];
         if (!col_ok || pix < 0 || (p.debug & 1)) continue;
         if constexpr (OUT_F32) {
@@ -231,19 +223,16 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
           cq[2] = fmaf(o.z, o.z, cq[2]); cq[3] = fmaf(o.w, o.w, cq[3]);
         }
       }
-      if constexpr (HAS_ADD) {
-        if (k + NBUF < MAXC) load_add(radd[k % NBUF], cpar + (k + NBUF) * CSTEP);   // this buffer is free again
-      }
       if (p.chan_stats && stat_slot >= 0) {
         // GroupNorm statistics for the consumer of this tensor (mdx_groupnorm_pre): reduce the 8 lanes that hold
         // the same 4 columns (lane = 4*row_lane + q4); lanes 0..3 store the warp's partial sums into its own slot —
         // no atomics, every slot is written exactly once, the consumer adds the slots in a fixed order
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
+        for (int k = 0; k < 4; ++k) {
 #pragma unroll
           for (int m = 4; m < 32; m <<= 1) {
-            cs[kk] += __shfl_xor_sync(0xffffffffu, cs[kk], m);
-            cq[kk] += __shfl_xor_sync(0xffffffffu, cq[kk], m);
+            cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], m);
+            cq[k] += __shfl_xor_sync(0xffffffffu, cq[k], m);
           }
         }
         if (lane < 4 && col_ok) {
@@ -252,11 +241,222 @@ __device__ __forceinline__ void epi_tile(const TcParams& p, uint32_t taddr, uint
           *reinterpret_cast<float4*>(dst + p.N) = make_float4(cq[0], cq[1], cq[2], cq[3]);
         }
       }
+      if constexpr (HAS_ADD) {
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) { radd[pass] = rnext[pass]; rnext[pass] = rnext2[pass]; }
+      }
     }
   }
 }
 
-template <int BN>
+// ------------------------------------------------------------------------------------------------------
+// Lean epilogue for the layers whose tiles are epilogue-bound (small K: the transformer's projections, the 1x1
+// convs): fp32 or bf16 output, optional residual (fp32 trunk or bf16), optional per-image bias row (emb add),
+// optional GroupNorm statistics; no activation.  Same data flow as epi_tile's general path (16-column chunks
+// through the per-warp staging tile), but
+//   * everything that does not change from chunk to chunk is computed once per tile: the four row pointers of a
+//     lane for `out` and `residual`, the row-validity mask, the bias pointers;
+//   * the variants are template parameters instead of run-time branches inside the chunk loop;
+//   * one residual buffer, refilled for the next chunk as soon as the current chunk has consumed it (no buffer is
+//     ever copied: a register move of a pending load's destination waits for the load); the first chunk's residual
+//     is requested before the accumulator wait.
+// The general path executes ~600 instructions per chunk and warp — with three epilogue warps per scheduler the
+// instruction stream itself, not HBM, set the tile time of the K = 320 layers; this one executes ~100.
+// ------------------------------------------------------------------------------------------------------
+template <int RES>
+__device__ __forceinline__ void res_load(uint4 (&q)[4], const char* base, const uint32_t (&ro)[4], int eoff, uint32_t ok) {
+  constexpr int RSZ = RES == 1 ? 4 : 2;
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) {
+    if ((ok >> pass) & 1u) {
+      const char* src = base + (size_t)(ro[pass] + (uint32_t)eoff) * RSZ;
+      if constexpr (RES == 1) {
+        q[pass] = __ldg(reinterpret_cast<const uint4*>(src));
+      } else {
+        const uint2 t = __ldg(reinterpret_cast<const uint2*>(src));
+        q[pass].x = t.x;
+        q[pass].y = t.y;
+      }
+    }
+  }
+}
+
+#ifndef MDX_EPI_NBUF
+#define MDX_EPI_NBUF 2      // residual chunks in flight per warp (named buffers; A/B: 1, 2, 3)
+#endif
+
+// Per-tile state of one epilogue warp on the lean path.
+struct EpiFastCtx {
+  uint32_t oo[4], ro[4];     // element offsets of this lane's four rows in out / residual (first column of chunk 0)
+  uint32_t ok;               // bit `pass` set: that row exists
+  char* obase;
+  const char* rbase;
+  const float* bp;           // bias + first column, or NULL
+  const float* rbp;          // per-image bias row + first column, or NULL
+  float* stats;              // chan_stats slot + first column, or NULL
+  int N;
+  uint32_t taddr, stg;
+  int lane, sr8, q4;
+};
+
+// One 16-column chunk `c`: accumulator -> staging tile -> coalesced rows (+ bias, + residual `cur`) -> global.
+template <bool OUT_F32, int RES, bool STATS>
+__device__ __forceinline__ void epi_fast_chunk(const EpiFastCtx& x, int c, const uint4 (&cur)[4]) {
+  constexpr int OSZ = OUT_F32 ? 4 : 2;
+  uint32_t r[16];
+  tmem_ld16(x.taddr + c * 16, r);
+  float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (x.bp) bz = __ldg(reinterpret_cast<const float4*>(x.bp + c * 16));
+  if (x.rbp) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(x.rbp + c * 16));
+    bz.x += t.x; bz.y += t.y; bz.z += t.z; bz.w += t.w;
+  }
+  tmem_ld_wait();
+  __syncwarp();   // the previous chunk's coalesced reads of the staging tile are done
+#pragma unroll
+  for (int j = 0; j < 4; ++j) sts128(x.stg + x.lane * 80 + 16 * j, r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+  __syncwarp();
+  float cs[4] = {0.f, 0.f, 0.f, 0.f}, cq[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) {
+    const uint4 u = lds128(x.stg + (pass * 8 + x.sr8) * 80 + x.q4 * 16);
+    float4 o = make_float4(__uint_as_float(u.x) + bz.x, __uint_as_float(u.y) + bz.y, __uint_as_float(u.z) + bz.z,
+                           __uint_as_float(u.w) + bz.w);
+    if constexpr (RES == 1) {
+      o.x += __uint_as_float(cur[pass].x); o.y += __uint_as_float(cur[pass].y);
+      o.z += __uint_as_float(cur[pass].z); o.w += __uint_as_float(cur[pass].w);
+    } else if constexpr (RES == 2) {
+      const float2 f0 = unpack_bf16x2(cur[pass].x), f1 = unpack_bf16x2(cur[pass].y);
+      o.x += f0.x; o.y += f0.y; o.z += f1.x; o.w += f1.y;
+    }
+    if ((x.ok >> pass) & 1u) {
+      char* dst = x.obase + (size_t)(x.oo[pass] + (uint32_t)(c * 16)) * OSZ;
+      if constexpr (OUT_F32) {
+        *reinterpret_cast<float4*>(dst) = o;
+      } else {
+        uint2 w;
+        w.x = pack_bf16x2(o.x, o.y);
+        w.y = pack_bf16x2(o.z, o.w);
+        *reinterpret_cast<uint2*>(dst) = w;
+        if constexpr (STATS) {   // the statistics are those of the values a reader of `out` sees
+          const float2 lo = unpack_bf16x2(w.x), hi = unpack_bf16x2(w.y);
+          o = make_float4(lo.x, lo.y, hi.x, hi.y);
+        }
+      }
+      if constexpr (STATS) {
+        cs[0] += o.x; cs[1] += o.y; cs[2] += o.z; cs[3] += o.w;
+        cq[0] = fmaf(o.x, o.x, cq[0]); cq[1] = fmaf(o.y, o.y, cq[1]);
+        cq[2] = fmaf(o.z, o.z, cq[2]); cq[3] = fmaf(o.w, o.w, cq[3]);
+      }
+    }
+  }
+  if constexpr (STATS) {
+    if (x.stats) {   // as in epi_tile: 8 lanes share 4 columns; lanes 0..3 store the warp's partial sums for its slot
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+#pragma unroll
+        for (int m = 4; m < 32; m <<= 1) {
+          cs[k] += __shfl_xor_sync(0xffffffffu, cs[k], m);
+          cq[k] += __shfl_xor_sync(0xffffffffu, cq[k], m);
+        }
+      }
+      if (x.lane < 4) {
+        float* dst = x.stats + c * 16;
+        *reinterpret_cast<float4*>(dst) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+        *reinterpret_cast<float4*>(dst + x.N) = make_float4(cq[0], cq[1], cq[2], cq[3]);
+      }
+    }
+  }
+}
+
+template <int BN, bool OUT_F32, int RES, bool STATS>
+__device__ __forceinline__ void epi_fast(const TcParams& p, uint32_t taddr, uint32_t stg, int lane, int cpar, int n_tile,
+                                         long long pix_own, long long stat_slot, const float* rb_row,
+                                         uint64_t* tfull_bar, uint32_t tfull_parity) {
+  constexpr int CSTEP = TcCfg<BN>::EPI_WARPS / 4;
+  EpiFastCtx x;
+  x.lane = lane; x.sr8 = lane >> 2; x.q4 = lane & 3;
+  x.taddr = taddr; x.stg = stg; x.N = p.N;
+  const int colbase = n_tile * BN + x.q4 * 4;               // this lane's first column of chunk 0
+  int nch = p.N - n_tile * BN;                               // 16-column chunks of this tile inside N (N % 16 == 0)
+  nch = (nch > BN ? BN : nch) >> 4;
+  x.ok = 0;
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) {
+    const long long pix = __shfl_sync(0xffffffffu, pix_own, pass * 8 + x.sr8);
+    if (pix >= 0) x.ok |= 1u << pass;
+    const long long pp = pix < 0 ? 0 : pix;
+    x.oo[pass] = (uint32_t)(pp * p.ldc + colbase);           // (the host admits this path only while they fit 32 bits)
+    x.ro[pass] = RES ? (uint32_t)(pp * p.ldr + colbase) : 0u;
+  }
+  x.obase = reinterpret_cast<char*>(p.out);
+  x.rbase = reinterpret_cast<const char*>(p.residual);
+  x.bp = p.bias ? p.bias + colbase : nullptr;
+  x.rbp = rb_row ? rb_row + colbase : nullptr;
+  x.stats = (STATS && stat_slot >= 0) ? p.chan_stats + (long long)stat_slot * 2 * p.N + colbase : nullptr;
+  int c = cpar;
+  // Residual buffers: MDX_EPI_NBUF named register sets, filled NBUF - 1 chunks ahead (with one buffer: refilled right
+  // after it was consumed).  The chunk loop is unrolled NBUF times, so a buffer is never copied — a register move of
+  // a pending load's destination would wait for the load.  The first chunks' loads go out before the accumulator
+  // wait: nothing in them depends on the MMAs.
+  uint4 ra[4];
+#if MDX_EPI_NBUF >= 2
+  uint4 rb[4];
+#endif
+#if MDX_EPI_NBUF >= 3
+  uint4 rc[4];
+#endif
+  auto load = [&](uint4 (&q)[4], int cc) __attribute__((always_inline)) {
+    if constexpr (RES != 0) {
+      if (cc < nch) res_load<RES>(q, x.rbase, x.ro, cc * 16, x.ok);
+    }
+  };
+  load(ra, c);
+#if MDX_EPI_NBUF >= 3
+  load(rb, c + CSTEP);
+#endif
+  mbar_wait(tfull_bar, tfull_parity);
+  tc_fence_after();
+#pragma unroll 1
+  for (;;) {
+#if MDX_EPI_NBUF == 1
+    if (c >= nch) break;
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, ra);
+    load(ra, c + CSTEP);
+    c += CSTEP;
+#elif MDX_EPI_NBUF == 2
+    if (c >= nch) break;
+    load(rb, c + CSTEP);
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, ra);
+    c += CSTEP;
+    if (c >= nch) break;
+    load(ra, c + CSTEP);
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, rb);
+    c += CSTEP;
+#else
+    if (c >= nch) break;
+    load(rc, c + 2 * CSTEP);
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, ra);
+    c += CSTEP;
+    if (c >= nch) break;
+    load(ra, c + 2 * CSTEP);
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, rb);
+    c += CSTEP;
+    if (c >= nch) break;
+    load(rb, c + 2 * CSTEP);
+    epi_fast_chunk<OUT_F32, RES, STATS>(x, c, rc);
+    c += CSTEP;
+#endif
+  }
+}
+
+// Epilogue kinds: each is its own kernel instantiation, so the register allocation and code of one epilogue do not
+// weigh on another.  EPI_FAST + (OUT_F32 * 6 + RES * 2 + STATS) selects an epi_fast variant.
+constexpr int EPI_GENERIC = 0;   // plain bf16 store, activations, profiling switches, ragged per-image bias (epi_tile)
+constexpr int EPI_GEGLU = 1;
+constexpr int EPI_FAST = 2;
+
+template <int BN, int EPI>
 __global__ void __launch_bounds__(TcCfg<BN>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB,
@@ -436,9 +636,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         stat_slot = (long long)img * p.stat_slots + in_img * 4 + qw;
       }
 
-      if (p.debug & 2) {
-        mbar_wait(&tfull[as], aph);  // profiling only: drop the tile
-      } else if (p.geglu) {
+      if constexpr (EPI >= EPI_FAST) {
+        constexpr int V = EPI - EPI_FAST;
+#ifdef MDX_EPI_L2PF
+        if ((V % 6) / 2 != 0 && cpar == 0) {   // next tile's residual rows on their way from HBM to L2
+          int m2, n2;
+          if (tile_at(it + 1, m2, n2)) {
+            const int x2 = (m2 % p.tiles_x) * p.tw + xl;
+            const int y2 = ((m2 / p.tiles_x) % p.tiles_y) * p.th + yl;
+            const int i2 = (m2 / tiles_per_img_grid) * p.tn + nl;
+            if (x2 < p.W && y2 < p.H && i2 < p.n_img) {
+              const long long pix2 = p.up ? ((long long)i2 * 2 * p.H + 2 * y2 + p.up_py) * (2 * p.W) + 2 * x2 + p.up_px
+                                          : ((long long)i2 * p.H + y2) * p.W + x2;
+              const int col2 = n2 * BN;
+              const int ncols = (p.N - col2) < BN ? (p.N - col2) : BN;
+              const int esz = p.res_f32 ? 4 : 2;
+              const char* src = reinterpret_cast<const char*>(p.residual) + (pix2 * p.ldr + col2) * esz;
+              asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"((uint32_t)(ncols * esz)) : "memory");
+            }
+          }
+        }
+#endif
+        // (tn == 1 whenever a per-image bias takes this path: the tile's 128 rows belong to one image)
+        const float* rb_row = p.rowbias ? p.rowbias + (long long)(m_tile / tiles_per_img_grid) * p.ld_rowbias : nullptr;
+        epi_fast<BN, (V / 6) != 0, (V % 6) / 2, (V % 2) != 0>(p, taddr, stg, lane, cpar, n_tile, pix_own, stat_slot, rb_row,
+                                                             &tfull[as], aph);
+      } else if constexpr (EPI == EPI_GEGLU) {
         mbar_wait(&tfull[as], aph);
         tc_fence_after();
         // GEGLU: the tile holds [BN/2 value columns | the matching BN/2 gate columns].  In the row-owner layout a
@@ -508,6 +731,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (cok && pix >= 0 && !(p.debug & 1)) *reinterpret_cast<uint4*>(obase + pix * p.ldc) = w;
           }
         }
+      } else if (p.debug & 2) {
+        mbar_wait(&tfull[as], aph);  // profiling only: drop the tile
       } else if (p.out_f32) {
         if (has_add) epi_tile<BN, true, true>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
         else epi_tile<BN, true, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
@@ -609,14 +834,22 @@ void pick_tile(int W, int H, int n, int* tw_, int* th_, int* tn_) {
 
 int num_sms() { return mdx_num_sms(); }
 
-template <int BN>
-int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p, cudaStream_t st) {
+template <int BN, int EPI>
+int launch_tc_epi(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& q, int grid, cudaStream_t st) {
   static MdxPerDeviceOnce attr;
   if (attr.need()) {
-    MDX_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         TcCfg<BN>::SMEM_BYTES));
     attr.mark();
   }
+  gemm_tc_kernel<BN, EPI><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
+  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
+  MDX_CHECK_LAUNCH();
+  return MDX_OK;
+}
+
+template <int BN>
+int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p, cudaStream_t st) {
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   TcParams q = p;
   if (const char* dbg = getenv("MDX_GEMM_DEBUG")) q.debug = atoi(dbg);
@@ -627,10 +860,23 @@ int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p,
     q.b_resident = 1;
     grid = (num_sms() / p.n_tiles_n) * p.n_tiles_n;
   }
-  gemm_tc_kernel<BN><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
-  g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
-  MDX_CHECK_LAUNCH();
-  return MDX_OK;
+  if (q.geglu) return launch_tc_epi<BN, EPI_GEGLU>(maps, mb, q, grid, st);
+  // epi_fast: no activation, no profiling switch, a per-image bias only when a tile never straddles two images, row
+  // offsets that fit 32 bits; the plain bf16 store (no add, no statistics) stays on epi_tile's 32-column path
+  const bool has_add = q.residual != nullptr || q.rowbias != nullptr || q.chan_stats != nullptr;
+  const long long rows_out = (long long)q.n_img * q.hw_out;
+  const bool fast_ok = q.act == 0 && q.debug == 0 && (q.rowbias == nullptr || q.tn == 1) && (q.out_f32 || has_add) &&
+                       rows_out * q.ldc < (1ll << 32) && (q.residual == nullptr || rows_out * q.ldr < (1ll << 32)) &&
+                       getenv("MDX_GEMM_NO_FAST_EPI") == nullptr;
+  if (!fast_ok) return launch_tc_epi<BN, EPI_GENERIC>(maps, mb, q, grid, st);
+  const int v = (q.out_f32 ? 6 : 0) + (q.residual ? (q.res_f32 ? 1 : 2) : 0) * 2 + (q.chan_stats ? 1 : 0);
+  switch (v) {
+#define MDX_TC_CASE(V) case V: return launch_tc_epi<BN, EPI_FAST + V>(maps, mb, q, grid, st);
+    MDX_TC_CASE(1) MDX_TC_CASE(2) MDX_TC_CASE(3) MDX_TC_CASE(4) MDX_TC_CASE(5) MDX_TC_CASE(6) MDX_TC_CASE(7)
+    MDX_TC_CASE(8) MDX_TC_CASE(9) MDX_TC_CASE(10) MDX_TC_CASE(11)
+#undef MDX_TC_CASE
+    default: return launch_tc_epi<BN, EPI_GENERIC>(maps, mb, q, grid, st);
+  }
 }
 
 }  // namespace
