@@ -24,6 +24,22 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 
+// Division by a run-time constant as multiply-high + shift (dividends < 2^31): the tile -> (image, y, x) arithmetic
+// runs once per tile in every epilogue warp, and a hardware-less integer divide is ~30 instructions.
+struct FastDiv {
+  uint32_t d, mul, shr;
+};
+inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  uint32_t s = 0;
+  while ((1ull << s) < d) ++s;                                   // ceil(log2 d)
+  f.mul = (uint32_t)(((1ull << 32) * ((1ull << s) - d)) / d + 1);
+  f.shr = s;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t x, const FastDiv& f) { return (__umulhi(x, f.mul) + x) >> f.shr; }
+
 struct TcParams {
   int nseg;
   int seg_kb[3];    // 64-wide channel blocks per tap
@@ -35,6 +51,7 @@ struct TcParams {
   int n_img, H, W;
   int tn, th, tw;
   int tiles_x, tiles_y;
+  FastDiv fd_tx, fd_ty, fd_tpi, fd_ntn;   // tiles_x, tiles_y, tiles_x * tiles_y, n_tiles_n
   int N, n_tiles_n, num_tiles;
   int m_tiles;
   float* chan_stats;   // optional [n_img][slots][2][N]: per-(image, 32-row slot, channel) sum / sum of squares of the
@@ -517,8 +534,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
     const long long tile = (long long)blockIdx.x + (long long)it * gridDim.x;
     if (tile >= p.num_tiles) return false;
-    n_tile = (int)(tile % p.n_tiles_n);
-    m_tile = (int)(tile / p.n_tiles_n);
+    m_tile = (int)fdiv((uint32_t)tile, p.fd_ntn);
+    n_tile = (int)tile - m_tile * p.n_tiles_n;
     return true;
   };
 
@@ -539,9 +556,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       }
       const uint32_t stage_tx = p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + Cfg::B_STAGE_BYTES;
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
-        const int x0 = (m_tile % p.tiles_x) * p.tw;
-        const int y0 = ((m_tile / p.tiles_x) % p.tiles_y) * p.th;
-        const int n0 = (m_tile / tiles_per_img_grid) * p.tn;
+        const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);
+        const int x0 = (m_tile - m_row * p.tiles_x) * p.tw;
+        const int y0 = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th;
+        const int n0 = (int)fdiv((uint32_t)m_tile, p.fd_tpi) * p.tn;
         int kcoord = 0;
         for (int seg = 0; seg < p.nseg; ++seg) {
           const CUtensorMap* tm = seg == 0 ? &tmA0 : (seg == 1 ? &tmA1 : &tmA2);
@@ -616,12 +634,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const bool has_add = p.residual != nullptr || p.rowbias != nullptr || p.chan_stats != nullptr;
     uint32_t iter = 0;
     int m_tile, n_tile;
+    // GEGLU: the bias slice of this warp's unit stays in registers while the n-tile does not change (weight-resident
+    // schedule: the whole kernel) — a global load at the top of every unit sat on the critical path of the epilogue
+    [[maybe_unused]] float g_blv = 0.f, g_blg = 0.f;
+    [[maybe_unused]] int g_bias_key = -1;
     for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
       const uint32_t as = iter & 1;
       const uint32_t aph = (iter >> 1) & 1;
-      const int x = (m_tile % p.tiles_x) * p.tw + xl;
-      const int y = ((m_tile / p.tiles_x) % p.tiles_y) * p.th + yl;
-      const int n = (m_tile / tiles_per_img_grid) * p.tn + nl;
+      const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);             // m_tile / tiles_x
+      const int m_img = (int)fdiv((uint32_t)m_tile, p.fd_tpi);            // m_tile / (tiles_x * tiles_y)
+      const int x = (m_tile - m_row * p.tiles_x) * p.tw + xl;
+      const int y = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th + yl;
+      const int n = m_img * p.tn + nl;
       const bool valid = (x < p.W) && (y < p.H) && (n < p.n_img);
       const long long pix_own = !valid ? -1
                                 : (p.up ? ((long long)n * 2 * p.H + 2 * y + p.up_py) * (2 * p.W) + 2 * x + p.up_px
@@ -631,8 +655,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       // statistics slot of this warp's 32 rows: (image, [phase,] tile inside the image, lane quadrant); tn == 1
       long long stat_slot = -1;
       if (p.chan_stats) {
-        const int img = m_tile / tiles_per_img_grid;
-        const int in_img = (p.up ? (p.up_py * 2 + p.up_px) * tiles_per_img_grid : 0) + m_tile % tiles_per_img_grid;
+        const int img = m_img;
+        const int in_img = (p.up ? (p.up_py * 2 + p.up_px) * tiles_per_img_grid : 0) + (m_tile - m_img * tiles_per_img_grid);
         stat_slot = (long long)img * p.stat_slots + in_img * 4 + qw;
       }
 
@@ -658,7 +682,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         }
 #endif
         // (tn == 1 whenever a per-image bias takes this path: the tile's 128 rows belong to one image)
-        const float* rb_row = p.rowbias ? p.rowbias + (long long)(m_tile / tiles_per_img_grid) * p.ld_rowbias : nullptr;
+        const float* rb_row = p.rowbias ? p.rowbias + (long long)m_img * p.ld_rowbias : nullptr;
         epi_fast<BN, (V / 6) != 0, (V % 6) / 2, (V % 2) != 0>(p, taddr, stg, lane, cpar, n_tile, pix_own, stat_slot, rb_row,
                                                              &tfull[as], aph);
       } else if constexpr (EPI == EPI_GEGLU) {
@@ -682,11 +706,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           const int ocol0 = ocol_tile + ucol;
           if (ocol0 >= n_out) break;
           const float* bvp = p.bias + n_tile * BN + ucol;   // bias is packed like the weight rows
-          float blv = 0.f, blg = 0.f;                       // lane <-> column; broadcast through smem below
-          if (p.bias && lane < uw) {
-            blv = __ldg(bvp + lane);
-            blg = __ldg(bvp + HALF + lane);
+          const int bias_key = n_tile * NU + u;
+          if (bias_key != g_bias_key) {                     // lane <-> column; broadcast through smem below
+            g_bias_key = bias_key;
+            g_blv = 0.f;
+            g_blg = 0.f;
+            if (p.bias && lane < uw) {
+              g_blv = __ldg(bvp + lane);
+              g_blg = __ldg(bvp + HALF + lane);
+            }
           }
+          const float blv = g_blv, blg = g_blg;
           uint32_t rv[32], rg[32];
           if (uw == 32) {
             tmem_ld32(taddr + ucol, rv);
@@ -966,9 +996,13 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   pick_tile(a->W, a->H, a->n_img, &p.tw, &p.th, &p.tn);
   p.tiles_x = (a->W + p.tw - 1) / p.tw;
   p.tiles_y = (a->H + p.th - 1) / p.th;
+  p.fd_tx = make_fastdiv((uint32_t)p.tiles_x);
+  p.fd_ty = make_fastdiv((uint32_t)p.tiles_y);
+  p.fd_tpi = make_fastdiv((uint32_t)(p.tiles_x * p.tiles_y));
   int tiles_n = (a->n_img + p.tn - 1) / p.tn;
   p.N = a->N;
   p.n_tiles_n = (a->N + bn - 1) / bn;
+  p.fd_ntn = make_fastdiv((uint32_t)p.n_tiles_n);
   long long nt = (long long)p.tiles_x * p.tiles_y * tiles_n * p.n_tiles_n;
   MDX_CHECK_ARG(nt < (1ll << 31), "mdx_gemm_tc: too many tiles");
   p.num_tiles = (int)nt;

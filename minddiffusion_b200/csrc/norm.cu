@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "../../include/mdx.h"
 #include <atomic>
+#include <stdlib.h>
 
 extern std::atomic<long long> g_mdx_launches;
 
@@ -153,8 +154,11 @@ __global__ void __launch_bounds__(512) gn_stats_kernel(const GnP p) {
     atomicAdd(&p.stats[(long long)img * p.groups * 2 + i], (&bins[0][0])[i]);
 }
 
+#ifndef MDX_GN_APPLY_BLOCKS
+#define MDX_GN_APPLY_BLOCKS 2   // resident blocks per SM the apply kernel is compiled for (register cap 64 at 2)
+#endif
 template <typename T, typename TO, bool SILU>
-__global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
+__global__ void __launch_bounds__(512, MDX_GN_APPLY_BLOCKS) gn_apply_kernel(const GnP p) {
   constexpr int V = 8;
   const int cv = threadIdx.x % p.CV, rl = threadIdx.x / p.CV;
   const int c0 = cv * V;
@@ -204,13 +208,16 @@ __global__ void __launch_bounds__(512) gn_apply_kernel(const GnP p) {
     }
     Vec<TO>::store(obase + (long long)row * p.ldo, v);
   };
+  // rows in flight per thread: 4 x 16 B for bf16 input, 2 x 32 B for fp32 input (the same bytes; the fp32 rows cost
+  // twice the registers, and the kernel has to stay within 64 registers to keep two blocks resident per SM)
+  constexpr int U = sizeof(T) == 2 ? 4 : 2;
   int r = r0 + rl;
-  for (; r + 3 * RP < r1; r += 4 * RP) {
-    float v[4][V];
+  for (; r + (U - 1) * RP < r1; r += U * RP) {
+    float v[U][V];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) Vec<T>::load(base + (long long)(r + u * RP) * ld, v[u]);
+    for (int u = 0; u < U; ++u) Vec<T>::load(base + (long long)(r + u * RP) * ld, v[u]);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) finish(r + u * RP, v[u]);
+    for (int u = 0; u < U; ++u) finish(r + u * RP, v[u]);
   }
   for (; r < r1; r += RP) {
     float v[V];
@@ -349,10 +356,12 @@ int launch_gn(GnP p, cudaStream_t st) {
   MDX_CHECK_ARG(p.CV <= 512, "mdx_groupnorm: too many channels (%d)", C);
   p.RP = 512 / p.CV;
   if (p.RP > 16) p.RP = 16;
-  // about eight waves of blocks (4 resident per SM), so the last, partly filled wave costs a few per cent instead of
-  // a third; each block walks at least 8*RP rows (4-deep unrolled loads twice)
+  // a few waves of blocks (MDX_GN_APPLY_BLOCKS resident per SM): enough that the last, partly filled wave is cheap,
+  // few enough that a block's prologue (statistics -> per-channel scale / shift) is amortised over many rows; each
+  // block walks at least 8*RP rows (4-deep unrolled loads twice)
   int chunks = (p.HW + 8 * p.RP - 1) / (8 * p.RP);
-  int want = (32 * mdx_num_sms() + p.n - 1) / p.n;
+  static const int waves = getenv("MDX_GN_WAVES") ? atoi(getenv("MDX_GN_WAVES")) : 4;   // A/B switch
+  int want = (MDX_GN_APPLY_BLOCKS * waves * mdx_num_sms() + p.n - 1) / p.n;
   if (chunks > want) chunks = want;
   if (chunks < 1) chunks = 1;
   p.rows_per_block = (p.HW + chunks - 1) / chunks;
