@@ -56,27 +56,42 @@ class CfgPairSplit:
                 if p == self.pair:
                     self.group = g
         self.n_pairs = self.world // 2
+        # MDX_SPLIT_IN_GRAPH=1: the all-gather is captured inside the step graph (one graph per step); default: it is
+        # issued between two captured segments of the step
+        import os
+        self.in_graph = os.environ.get("MDX_SPLIT_IN_GRAPH", "0") == "1"
 
     def my_context(self, cond, uncond):
         return cond if self.is_cond else uncond
 
+    def pack(self, eps_local, packed, channels):
+        """The first `channels` entries of every row of eps_local ([B, h, w, ld]: the tensor-core conv_out pads its 4
+        output channels to 16 columns) into packed [B, h, w, channels] with one strided row copy, so that a quarter of
+        the bytes cross NVLink."""
+        ld = eps_local.shape[-1]
+        if ld == channels:
+            packed.copy_(eps_local)
+        elif eps_local.is_cuda and (channels * eps_local.element_size()) % 16 == 0:
+            from . import ops
+            ops.copy_rows(eps_local.view(1, -1, ld)[:, :, :channels], packed.view(1, -1, channels))
+        else:
+            packed.copy_(eps_local[..., :channels])
+        return packed
+
+    def all_gather(self, packed, out):
+        """out[2B, ...] = [unconditional rank's packed | conditional rank's packed]: one NCCL all-gather into a
+        contiguous tensor (rank order = pair order = the concat order of plms.py:192-194)."""
+        dist.all_gather_into_tensor(out, packed, group=self.group)
+        return out
+
     def exchange(self, eps_local, out=None, channels=None):
         """eps_local: this rank's UNet output [B, ...].  Returns [2B, ...] with the unconditional half first — the
-        row order the fused combine+update kernel expects (the concat order of plms.py:192-194).
-
-        channels: only the first `channels` entries of the last dim carry data (the tensor-core conv_out pads its 4
-        output channels to 16 columns): they are packed into [B, ..., channels] with one strided row copy before the
-        exchange, so 1/4 of the bytes cross NVLink.  One NCCL all-gather into a contiguous tensor — capturable in a
-        CUDA graph, which is how the step plans of samplers.py issue it."""
+        row order the fused combine+update kernel expects.  channels: see pack()."""
         eps_local = eps_local.contiguous()
-        ld = eps_local.shape[-1]
-        if channels is not None and channels != ld and eps_local.is_cuda and (channels * eps_local.element_size()) % 16 == 0:
-            from . import ops
-            packed = torch.empty(tuple(eps_local.shape[:-1]) + (channels,), dtype=eps_local.dtype, device=eps_local.device)
-            ops.copy_rows(eps_local.view(1, -1, ld)[:, :, :channels], packed.view(1, -1, channels))
-            eps_local = packed
-        B = eps_local.shape[0]
+        if channels is not None and channels != eps_local.shape[-1]:
+            eps_local = self.pack(eps_local, torch.empty(tuple(eps_local.shape[:-1]) + (channels,), dtype=eps_local.dtype,
+                                                         device=eps_local.device), channels)
         if out is None:
-            out = torch.empty((2 * B,) + tuple(eps_local.shape[1:]), dtype=eps_local.dtype, device=eps_local.device)
-        dist.all_gather_into_tensor(out, eps_local, group=self.group)
-        return out
+            out = torch.empty((2 * eps_local.shape[0],) + tuple(eps_local.shape[1:]), dtype=eps_local.dtype,
+                              device=eps_local.device)
+        return self.all_gather(eps_local, out)

@@ -105,6 +105,10 @@ class _StepPlan:
         self.counter = torch.zeros(1, dtype=torch.int32, device=dev)
         self.repeat = 2 if (cfg and split is None) else 1
         self.t = torch.zeros(B * self.repeat, dtype=torch.float32, device=dev)
+        self.model_out = None
+        if split is not None:   # eps halves: this rank's (4 real channels of the padded conv_out) and the pair's
+            self.packed = torch.zeros((B, H, W, C), dtype=torch.float32, device=dev)
+            self.xbuf = torch.zeros((2 * B, H, W, C), dtype=torch.float32, device=dev)
         self.graphs = {}
         if unet._ctx is None or unet._ctx["n"] != B * self.repeat:
             raise ValueError("context batch does not match the latent batch")
@@ -119,56 +123,92 @@ class _StepPlan:
             h.zero_()
 
     # ---- launch sequences (identical eager and under capture) ----
+    # A phase is a list of segments.  Without the CFG pair split (or with split.in_graph) it is ONE segment; with it,
+    # the NCCL exchange of the eps halves sits between two captured segments and is issued eagerly.
     def _eval(self, x):
         ops.gather_row(self.t_table, self.counter, self.t)
-        out = self.unet._forward_impl(x, self.t, self.repeat, None, True)
+        self.model_out = self.unet._forward_impl(x, self.t, self.repeat, None, True)
         if self.split is not None:
-            out = self.split.exchange(out, channels=self.C)
-        return out
+            self.split.pack(self.model_out, self.packed, self.C)
 
-    def _kernel(self, kind, out, **kw):
-        ops.sampler_step_ex(kind, out, self.img, kw.pop("x_out", self.img), self.C, self.cfg, self.scale,
-                            table=self.table, counter=self.counter, model_type=self.model_type, **kw)
+    def _exchange(self, dry=False):
+        if not dry:
+            self.split.all_gather(self.packed, self.xbuf)
+        self.model_out = self.xbuf
+
+    def _kernel(self, kind, x_out=None, **kw):
+        ops.sampler_step_ex(kind, self.model_out, self.img, self.img if x_out is None else x_out, self.C, self.cfg,
+                            self.scale, table=self.table, counter=self.counter, model_type=self.model_type, **kw)
         ops.step_advance(self.counter, 1)
 
-    def _run_first(self):
-        out = self._eval(self.img)
-        self._kernel("plms", out, x_out=self.x_tmp, e_t_out=self.hist[0])
-        out = self._eval(self.x_tmp)
-        self._kernel("plms", out, x_model=self.x_tmp, hist=(self.hist[0], None, None), pred_x0=self.pred_x0)
+    def _phase(self, phase):
+        """[(callable, is_exchange)] in launch order."""
+        ev = lambda x: ((lambda: self._eval(x)), False)
+        k = lambda kind, **kw: ((lambda: self._kernel(kind, **kw)), False)
+        xch = [(self._exchange, True)] if self.split is not None else []
+        if phase == "first":     # PLMS pseudo improved Euler: evaluate, Euler step to x_tmp, evaluate there, average
+            return ([ev(self.img)] + xch + [k("plms", x_out=self.x_tmp, e_t_out=self.hist[0]), ev(self.x_tmp)] + xch +
+                    [k("plms", x_model=self.x_tmp, hist=(self.hist[0], None, None), pred_x0=self.pred_x0)])
+        if phase == "multi":     # Adams-Bashforth 2 / 3 / 4 (weights in the table), history shifts in the kernel
+            return [ev(self.img)] + xch + [k("plms", hist=tuple(self.hist), shift_hist=True, pred_x0=self.pred_x0)]
+        if phase == "ddim":
+            return [ev(self.img)] + xch + [k("plms", noise=self.noise, pred_x0=self.pred_x0)]
+        if phase == "dpm":       # x0_cur overwrites x0_prev in place
+            return [ev(self.img)] + xch + [k("dpm", hist=(self.hist[0], None, None), pred_x0=self.hist[0])]
+        raise ValueError(phase)
 
-    def _run_multi(self):
-        self._kernel("plms", self._eval(self.img), hist=tuple(self.hist), shift_hist=True, pred_x0=self.pred_x0)
-
-    def _run_ddim(self):
-        self._kernel("plms", self._eval(self.img), noise=self.noise, pred_x0=self.pred_x0)
-
-    def _run_dpm(self):
-        self._kernel("dpm", self._eval(self.img), hist=(self.hist[0], None, None), pred_x0=self.hist[0])
+    def _segments(self, phase):
+        """Consecutive launches merged into capturable segments; an exchange is a segment of its own unless the split
+        asks for it inside the graph."""
+        in_graph = self.split is not None and self.split.in_graph
+        segs, cur = [], []
+        for fn, is_x in self._phase(phase):
+            if is_x and not in_graph:
+                if cur:
+                    segs.append(("launch", cur))
+                segs.append(("exchange", [fn]))
+                cur = []
+            else:
+                cur.append(fn)
+        if cur:
+            segs.append(("launch", cur))
+        return segs
 
     def run(self, phase):
-        fn = getattr(self, "_run_" + phase)
         if not self.unet.use_cuda_graph:
-            fn()
+            for fn, _ in self._phase(phase):
+                fn()
             return
         ent = self.graphs.get(phase)
         if ent is None:
-            # warm-up (kernel attributes, allocator) on a snapshot of the loop state, then capture; capture itself
-            # executes nothing
+            # warm-up (kernel attributes, allocator, NCCL) on a snapshot of the loop state, then capture segment by
+            # segment; capture itself executes nothing
             state = [self.img, self.x_tmp, self.pred_x0, self.counter] + self.hist
             saved = [t.clone() for t in state]
-            fn()
-            torch.cuda.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            n0 = _lib.launch_count()
-            with torch.cuda.graph(graph, pool=self.unet.graph_pool()):
+            for fn, _ in self._phase(phase):
                 fn()
-            ent = (graph, _lib.launch_count() - n0)
+            torch.cuda.synchronize()
+            ent = []
+            for kind, fns in self._segments(phase):
+                if kind == "exchange":
+                    fns[0](dry=True)       # only the bookkeeping: the next segment reads the gathered buffer
+                    ent.append((None, fns[0], 0))
+                    continue
+                graph = torch.cuda.CUDAGraph()
+                n0 = _lib.launch_count()
+                with torch.cuda.graph(graph, pool=self.unet.graph_pool()):
+                    for fn in fns:
+                        fn()
+                ent.append((graph, None, _lib.launch_count() - n0))
             self.graphs[phase] = ent
             for t, sv in zip(state, saved):
                 t.copy_(sv)
-        ent[0].replay()
-        self.unet.replayed_launches += ent[1]
+        for graph, eager, nk in ent:
+            if graph is None:
+                eager()
+            else:
+                graph.replay()
+                self.unet.replayed_launches += nk
 
 
 class _GuidedUNet:
