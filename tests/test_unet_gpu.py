@@ -362,10 +362,10 @@ def test_whole_step_graph_replay_matches_eager(which):
     cls = {"plms": samplers.PLMSSampler, "ddim": samplers.DDIMSampler, "dpm": samplers.DPMSolverSampler}[which]
     run = lambda S: cls(ldm).sample(S, 2, (4, 16, 16), c.cuda(), x_T=x_T.cuda(), verbose=False,
                                     unconditional_guidance_scale=7.5, unconditional_conditioning=uc)[0]
-    eager6, eager9 = run(6), run(9)
+    eager6, eager9 = run(5), run(10)   # (S must divide 1000: util.py:136-138 indexes alphas_cumprod[t + 1])
     model.use_cuda_graph = True
     n0 = model.replayed_launches
-    g6, g6b, g9 = run(6), run(6), run(9)
+    g6, g6b, g9 = run(5), run(5), run(10)
     assert model.replayed_launches > n0
     # GroupNorm sums of the 8x8 level use fp64 atomics: runs agree to rounding, not bit for bit
     assert rel_err(g6, eager6) < 2e-3 and rel_err(g6b, eager6) < 2e-3 and rel_err(g9, eager9) < 2e-3
