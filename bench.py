@@ -350,9 +350,11 @@ def run_b200(a):
         pair = {"value": B * (world // 2) * kp / (ms_pair / 1e3), "unit": "images/s", "steps": kp,
                 "ms_per_unet_eval": ms_pair / kp / S, "dp_ms_per_unet_eval": ms / a.steps / S,
                 "exchange_us": x0e.elapsed_time(x1e) * 1e3 / 20, "exchange_bytes_per_rank": B * h * h * 4 * 4,
-                "latents_identical_on_pair": identical, "in_graph": not a.no_graph,
-                "parallelism": "dp%d x cfg-pair-split (packed 4-channel eps all-gather over NCCL inside the step graph)"
-                               % (world // 2)}
+                "latents_identical_on_pair": identical, "cuda_graph": not a.no_graph,
+                "exchange_in_graph": bool(split.in_graph),
+                "parallelism": "dp%d x cfg-pair-split (packed 4-channel eps all-gather over NCCL, %s)"
+                               % (world // 2, "captured inside the step graph" if split.in_graph
+                                  else "issued between the two captured segments of a step")}
         ldm.cfg_split = None
 
     # ---- dominant kernel, live: every mdx_gemm_tc launch of one guided UNet evaluation ----
