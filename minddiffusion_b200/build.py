@@ -22,6 +22,8 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
 
 
 def _digest():
+    """Hash of the sources and the compile flags — with the checkout's own path taken out, so that the library built
+    in one checkout is recognised as current in a copy of it somewhere else (the GPU box)."""
     h = hashlib.sha256()
     names = sorted(os.listdir(CSRC)) + ["../../include/mdx.h"]
     for name in names:
@@ -29,20 +31,39 @@ def _digest():
         if os.path.isfile(path):
             h.update(name.encode())
             h.update(open(path, "rb").read())
-    h.update(" ".join(FLAGS).encode())
+    h.update(" ".join(FLAGS).replace(HERE, "<pkg>").encode())
     return h.hexdigest()
 
 
 def build(force=False, verbose=False):
     stamp = os.path.join(OBJ, "stamp")
     digest = _digest()
-    if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == digest:
+
+    def current():
+        return os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == digest
+
+    if not force and current():
         return LIB
     if not os.path.exists(NVCC):
         if os.path.exists(LIB):
             return LIB  # GPU box without a toolkit: use the prebuilt library that travelled with the repo
         raise RuntimeError("nvcc not found at %s and no prebuilt %s" % (NVCC, LIB))
     os.makedirs(OBJ, exist_ok=True)
+    # one builder at a time: the ranks of a multi-GPU launch all come through here, and a rank must never dlopen a
+    # library another rank is still linking.  The lock is advisory (flock); whoever gets it second finds the work done.
+    import fcntl
+    lock = open(os.path.join(OBJ, "lock"), "w")
+    fcntl.flock(lock, fcntl.LOCK_EX)
+    try:
+        if not force and current():
+            return LIB
+        return _build_locked(stamp, digest, verbose)
+    finally:
+        fcntl.flock(lock, fcntl.LOCK_UN)
+        lock.close()
+
+
+def _build_locked(stamp, digest, verbose):
 
     def compile_one(src):
         obj = os.path.join(OBJ, src.replace(".cu", ".o"))
@@ -56,10 +77,12 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static"]
+    tmp = LIB + ".tmp.%d" % os.getpid()
+    cmd = [NVCC, "-shared", "-o", tmp] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    os.replace(tmp, LIB)   # atomic: a reader sees the old library or the new one, never a partial file
     with open(stamp, "w") as f:
         f.write(digest)
     return LIB

@@ -56,7 +56,13 @@ def main():
             assert identical, "the two ranks of a pair drifted apart"
             assert rel < 2e-3, rel
     dist.barrier()
+    torch.cuda.synchronize()
     print("rank %d PAIR_SPLIT_OK" % rank, flush=True)
+    if ldm.cfg_split.in_graph:
+        # graphs that captured an NCCL collective keep the communicator busy: destroy_process_group() did not return
+        # on this stack (torch 2.11 / NCCL 2.28) while they were alive, so this rank leaves without the teardown
+        sys.stdout.flush()
+        os._exit(0)
     dist.destroy_process_group()
 
 
