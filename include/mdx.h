@@ -86,6 +86,10 @@ typedef struct mdx_gemm_args {
                   re-reads the activation.  No atomics: each slot is written once and the consumer adds the slots in
                   a fixed order.  The four up_phase launches of one tensor fill disjoint slots of one array.
                   Needs images of >= 128 pixels (mdx_gemm_tc_stat_slots returns 0 otherwise). */
+  int32_t stride; /* 0 / 1: as above.  2: the single 3x3 segment is a stride-2, pad-1 convolution (Downsample,
+                  openaimodel.py:80-88): H, W stay the INPUT image, out / residual / rowbias / chan_stats are addressed in
+                  the [n_img, (H-1)/2+1, (W-1)/2+1] output image (size chan_stats with those dimensions).  The taps are
+                  strided TMA boxes over the input; no patch matrix is built. */
 } mdx_gemm_args;
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
 /* Statistics slots per image for mdx_gemm_args.chan_stats (0: images too small, use the two-pass GroupNorm). */
@@ -214,8 +218,9 @@ int mdx_timestep_embedding(const float* t, int32_t n, int32_t dim, float max_per
  *  mdx_nhwc_to_nchw: x [n, H, W, C] (dtype) -> fp32 NCHW.
  *  mdx_upsample_nearest2x: ops.ResizeNearestNeighbor (openaimodel.py:53-60) on NHWC (fp32->bf16 converts).
  *  mdx_concat_channels: ops.Concat(axis=1) (openaimodel.py:567) on NHWC rows.
- *  mdx_im2col3x3: gathers 3x3 patches (stride, pad 1) into [n*OH*OW, 9*C] rows, K order (r,s,c) — feeds the
- *     stride-2 Downsample conv (openaimodel.py:80-88) to mdx_gemm_tc.
+ *  mdx_im2col3x3: gathers 3x3 patches (stride, pad 1) into [n*OH*OW, 9*C] rows, K order (r,s,c) — the patch-matrix
+ *     form of a strided conv (the UNet's Downsample now runs as mdx_gemm_args.stride = 2; kept for callers that
+ *     want the matrix).
  *  mdx_cast: elementwise fp32 <-> bf16 conversion of count elements. */
 int mdx_nchw_to_nhwc(const float* x, int32_t n, int32_t C, int32_t H, int32_t W, int32_t repeat, void* out,
                      int32_t dtype, void* stream);

@@ -42,6 +42,7 @@ class GemmArgs(ctypes.Structure):
         ("act", c_int),
         ("up_phase", c_int),
         ("chan_stats", c_p),
+        ("stride", c_int),
     ]
 
 

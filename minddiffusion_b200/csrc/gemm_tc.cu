@@ -46,6 +46,7 @@ struct TcParams {
   int seg_taps[3];  // 1, 9 (3x3) or 4 (2x2 window of one phase of a 2x-upsampled 3x3 conv)
   int up_py, up_px; // phase of the upsampled output this launch produces (taps == 4)
   int up;           // 1: output / residual rows are pixels (2y+py, 2x+px) of the [n, 2H, 2W] image
+  int stride;       // 1, or 2: H, W below are the OUTPUT image of a stride-2 3x3 conv (the A map strides the input)
   long long hw_out; // pixels per image in the output addressing
   int total_kb;
   int n_img, H, W;
@@ -571,7 +572,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             for (int cb = 0; cb < nkb; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
               mbar_arrive_expect_tx(&full[stage], stage_tx);
-              tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 + dx, y0 + dy, n0);
+              tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 * p.stride + dx, y0 * p.stride + dy, n0);
               if (!p.b_resident) tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
               kcoord += BK;
               if (++stage == STAGES) {
@@ -804,7 +805,10 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-int make_map_a(CUtensorMap* m, const void* ptr, long long ld, int C, int W, int H, int n, int tw, int th, int tn) {
+// W, H: the INPUT image; stride 2 makes the box step over every other pixel (TMA element strides), so that tap (r, s)
+// of a stride-2 convolution is one box load starting at (2 x0 + s - 1, 2 y0 + r - 1) — no im2col buffer
+int make_map_a(CUtensorMap* m, const void* ptr, long long ld, int C, int W, int H, int n, int tw, int th, int tn,
+               int stride = 1) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     mdx_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
@@ -812,8 +816,8 @@ int make_map_a(CUtensorMap* m, const void* ptr, long long ld, int C, int W, int 
   }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n};
   cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)W * ld * 2, (cuuint64_t)H * W * ld * 2};
-  cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)tw, (cuuint32_t)th, (cuuint32_t)tn};
-  cuuint32_t es[4] = {1, 1, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)(tw * stride), (cuuint32_t)(th * stride), (cuuint32_t)tn};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -992,10 +996,18 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   MDX_CHECK_ARG(bn == 64 || bn == 128 || bn == 160 || bn == 192 || bn == 256, "mdx_gemm_tc: unsupported block_n %d", bn);
   if (a->geglu) MDX_CHECK_ARG((a->N / 2) % (bn / 2) == 0, "mdx_gemm_tc: geglu needs N/2 %% (block_n/2) == 0");
 
-  p.n_img = a->n_img; p.H = a->H; p.W = a->W;
-  pick_tile(a->W, a->H, a->n_img, &p.tw, &p.th, &p.tn);
-  p.tiles_x = (a->W + p.tw - 1) / p.tw;
-  p.tiles_y = (a->H + p.th - 1) / p.th;
+  const int stride = a->stride == 2 ? 2 : 1;
+  MDX_CHECK_ARG(a->stride == 0 || a->stride == 1 || a->stride == 2, "mdx_gemm_tc: stride must be 1 or 2");
+  if (stride == 2)
+    MDX_CHECK_ARG(a->nseg == 1 && a->seg_taps[0] == 9 && !a->up_phase && !a->geglu,
+                  "mdx_gemm_tc: stride 2 needs one 3x3 segment (no up_phase, no geglu)");
+  // the image the tiles, the output rows and the statistics slots live in: the conv's output
+  const int OH = stride == 2 ? (a->H - 1) / 2 + 1 : a->H, OW = stride == 2 ? (a->W - 1) / 2 + 1 : a->W;
+  p.stride = stride;
+  p.n_img = a->n_img; p.H = OH; p.W = OW;
+  pick_tile(OW, OH, a->n_img, &p.tw, &p.th, &p.tn);
+  p.tiles_x = (OW + p.tw - 1) / p.tw;
+  p.tiles_y = (OH + p.th - 1) / p.th;
   p.fd_tx = make_fastdiv((uint32_t)p.tiles_x);
   p.fd_ty = make_fastdiv((uint32_t)p.tiles_y);
   p.fd_tpi = make_fastdiv((uint32_t)(p.tiles_x * p.tiles_y));
@@ -1008,7 +1020,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   p.num_tiles = (int)nt;
   p.m_tiles = p.tiles_x * p.tiles_y * tiles_n;
   if (a->chan_stats) {
-    MDX_CHECK_ARG(p.tn == 1, "mdx_gemm_tc: chan_stats needs images of at least 128 pixels (got %d x %d)", a->H, a->W);
+    MDX_CHECK_ARG(p.tn == 1, "mdx_gemm_tc: chan_stats needs images of at least 128 pixels (got %d x %d)", OH, OW);
     p.stat_slots = p.tiles_x * p.tiles_y * 4 * (a->up_phase ? 4 : 1);
   }
   p.out = a->out; p.ldc = a->ldc; p.out_f32 = a->out_dtype == MDX_F32;
@@ -1021,7 +1033,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     MDX_CHECK_ARG(!a->geglu && (reinterpret_cast<uintptr_t>(a->chan_stats) & 15) == 0,
                   "mdx_gemm_tc: chan_stats excludes geglu and must be 16-byte aligned");
   // (the slot count is checked below, once the tile shape is known)
-  p.hw_out = (long long)a->H * a->W;
+  p.hw_out = (long long)OH * OW;
   if (a->up_phase) {
     MDX_CHECK_ARG(a->up_phase >= 1 && a->up_phase <= 4 && a->nseg == 1 && a->seg_taps[0] == 4 && !a->geglu,
                   "mdx_gemm_tc: up_phase needs 1..4, one segment with 4 taps, no geglu");
@@ -1034,7 +1046,7 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
   CUtensorMap maps[3];
   for (int s = 0; s < 3; ++s) {
     int src = s < a->nseg ? s : 0;
-    int rc = make_map_a(&maps[s], a->a[src], a->lda[src], a->seg_c[src], a->W, a->H, a->n_img, p.tw, p.th, p.tn);
+    int rc = make_map_a(&maps[s], a->a[src], a->lda[src], a->seg_c[src], a->W, a->H, a->n_img, p.tw, p.th, p.tn, stride);
     if (rc) return rc;
   }
   CUtensorMap mb;

@@ -68,7 +68,7 @@ ACT = {None: 0, "gelu": 1, "quick_gelu": 2, "tanh": 3}
 
 
 def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, geglu=False, out_dtype=torch.bfloat16,
-            block_n=0, act=None, up_phase=0, chan_stats=None):
+            block_n=0, act=None, up_phase=0, chan_stats=None, stride=1):
     """Tensor-core implicit GEMM (mdx_gemm_tc).
 
     segs: list of (a, taps); a is bf16 ``[n, H, W, C]`` (conv view) or ``[M, C]`` (dense), taps 9 or 1.
@@ -99,7 +99,8 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
     if weight.shape[1] != ktot:
         raise ValueError("weight K=%d does not match segments K=%d" % (weight.shape[1], ktot))
     n_out = N // 2 if geglu else N
-    M = n_img * H * W * (4 if up_phase else 1)   # up_phase: out / residual are the 2x-upsampled image
+    OH, OW = ((H - 1) // 2 + 1, (W - 1) // 2 + 1) if stride == 2 else (H, W)   # stride 2: out is the strided conv's image
+    M = n_img * OH * OW * (4 if up_phase else 1)   # up_phase: out / residual are the 2x-upsampled image
     if up_phase and out is None:
         raise ValueError("up_phase launches write one phase of a caller-provided [n, 2H, 2W, N] buffer")
     if out is None:
@@ -130,8 +131,9 @@ def gemm_tc(segs, weight, out=None, bias=None, rowbias=None, residual=None, gegl
     args.block_n = block_n
     args.act = ACT[act]
     args.up_phase = up_phase
+    args.stride = stride
     if chan_stats is not None:
-        slots = stat_slots(n_img, H, W, bool(up_phase))
+        slots = stat_slots(n_img, OH, OW, bool(up_phase))
         if slots == 0 or chan_stats.dtype != torch.float32 or not chan_stats.is_contiguous() or (
                 tuple(chan_stats.shape) != (n_img, slots, 2, n_out)):
             raise ValueError("chan_stats must be contiguous float32 [n_img, %d, 2, %d]" % (slots, n_out))

@@ -106,6 +106,7 @@ class _StepPlan:
         self.repeat = 2 if (cfg and split is None) else 1
         self.t = torch.zeros(B * self.repeat, dtype=torch.float32, device=dev)
         self.model_out = None
+        self.emb_table = self.emb_row = None
         if split is not None:   # eps halves: this rank's (4 real channels of the padded conv_out) and the pair's
             self.packed = torch.zeros((B, H, W, C), dtype=torch.float32, device=dev)
             self.xbuf = torch.zeros((2 * B, H, W, C), dtype=torch.float32, device=dev)
@@ -118,6 +119,13 @@ class _StepPlan:
             raise ValueError("too many steps for a step plan")
         self.table[:len(rows)].copy_(torch.tensor(rows, dtype=torch.float32))
         self.t_table[:len(times)].copy_(torch.tensor(times, dtype=torch.float32))
+        # the timestep-embedding MLPs of every evaluation of the loop, in one batch (they depend only on t)
+        emb = self.unet.emb_rows(self.t_table[:len(times)])
+        if self.emb_table is None or self.emb_table.shape[1] != emb.shape[1]:
+            self.emb_table = torch.zeros((MAX_ROWS, emb.shape[1]), dtype=torch.float32, device=emb.device)
+            self.emb_row = torch.zeros((1, emb.shape[1]), dtype=torch.float32, device=emb.device)
+            self.graphs = {}
+        self.emb_table[:len(times)].copy_(emb)
         self.counter.zero_()
         for h in self.hist:
             h.zero_()
@@ -126,8 +134,8 @@ class _StepPlan:
     # A phase is a list of segments.  Without the CFG pair split (or with split.in_graph) it is ONE segment; with it,
     # the NCCL exchange of the eps halves sits between two captured segments and is issued eagerly.
     def _eval(self, x):
-        ops.gather_row(self.t_table, self.counter, self.t)
-        self.model_out = self.unet._forward_impl(x, self.t, self.repeat, None, True)
+        ops.gather_row(self.emb_table, self.counter, self.emb_row)     # this evaluation's embedding row
+        self.model_out = self.unet._forward_impl(x, self.t, self.repeat, None, True, emb_row=self.emb_row)
         if self.split is not None:
             self.split.pack(self.model_out, self.packed, self.C)
 

@@ -344,11 +344,11 @@ class UNetModel:
     def _down(self, pre, x):
         w, b = self.L[pre + "op"]
         n, H, W, C = x.shape
-        if self.bf16:
-            col = ops.im2col3x3(x, 2, out_dtype=self.dtype)      # [n, OH, OW, 9C]
-            OH, OW = col.shape[1], col.shape[2]
+        if self.bf16:   # the nine taps are strided TMA boxes over the bf16 copy of the trunk: no patch matrix
+            OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
             chan = self._chan(n, OH, OW, w.shape[0])
-            out = ops.gemm_tc([(col, 1)], w, bias=b, out_dtype=torch.float32, chan_stats=chan).view(n, OH, OW, -1)
+            out = ops.gemm_tc([(ops.cast(x, self.dtype), 9)], w, bias=b, out_dtype=torch.float32, chan_stats=chan,
+                              stride=2).view(n, OH, OW, -1)
             out._mdx_chan = chan
             return out
         return ops.conv_direct(x, w, 3, 3, 2, 1, bias=b)
@@ -421,19 +421,29 @@ class UNetModel:
             for li, layer in enumerate(block):
                 visit("output_blocks.%d.%d." % (bi, li), layer)
 
-    def _forward_impl(self, x_nchw, t, repeat, taps=None, uniform_t=False):
+    def emb_rows(self, t):
+        """timestep embedding -> time_embed MLP -> every ResBlock's emb_layers (openaimodel.py:548-549, 199-200), all
+        fp32: t [m] -> [m, sum of the ResBlocks' Cout].  The result depends on nothing but t, so a sampler loop
+        computes the rows of all its steps in one call before the loop (samplers._StepPlan)."""
+        L = self.L
+        t_emb = ops.timestep_embedding(t, self.model_channels)
+        emb = ops.conv_direct(t_emb, L["te0"][0], bias=L["te0"][1])
+        emb = ops.conv_direct(emb, L["te2"][0], bias=L["te2"][1], pre_silu=True)
+        return ops.conv_direct(emb, L["emb_all"][0], bias=L["emb_all"][1], pre_silu=True)
+
+    def _forward_impl(self, x_nchw, t, repeat, taps=None, uniform_t=False, emb_row=None):
         L = self.L
         n = x_nchw.shape[0] * repeat
         self._gn_scratch = torch.empty(n * 64, dtype=torch.float64, device=self.device)
-        # timestep embedding + time_embed MLP + every ResBlock's emb_layers, all fp32 (tiny).  The sampler loops
-        # evaluate the whole batch at ONE timestep (plms.py:118, ddim ts = full((b,), step)): one row is computed and
-        # every image reads it (row stride 0 of the per-image bias).
-        t_emb = ops.timestep_embedding(t[:1] if uniform_t else t, self.model_channels)
-        emb = ops.conv_direct(t_emb, L["te0"][0], bias=L["te0"][1])
-        emb = ops.conv_direct(emb, L["te2"][0], bias=L["te2"][1], pre_silu=True)
-        emb_all = ops.conv_direct(emb, L["emb_all"][0], bias=L["emb_all"][1], pre_silu=True)  # [n, sum Cout]
-        if uniform_t:
-            emb_all = emb_all.expand(n, -1)
+        # The sampler loops evaluate the whole batch at ONE timestep (plms.py:118, ddim ts = full((b,), step)): one
+        # embedding row is computed (or handed in: emb_row [1, sum Cout]) and every image reads it (row stride 0 of the
+        # per-image bias).
+        if emb_row is not None:
+            emb_all = emb_row.expand(n, -1)
+        else:
+            emb_all = self.emb_rows(t[:1] if uniform_t else t)  # [n, sum Cout]
+            if uniform_t:
+                emb_all = emb_all.expand(n, -1)
         if self._concat is not None:   # DiffusionWrapper 'concat' / 'hybrid' (wukong ddpm.py:363-372): cat((x, c_concat), 1)
             h = ops.nchw2_to_nhwc(x_nchw, self._concat, self.dtype, repeat=repeat, cpad=self.cin_pad)
         else:

@@ -35,7 +35,7 @@ def test_ctypes_structs_match_the_compiled_header():
     assert ctypes.sizeof(_lib.ConvArgs) == lib.mdx_sizeof_conv_args()
     assert ctypes.sizeof(_lib.StepArgs) == lib.mdx_sizeof_step_args()
     assert _lib.GemmArgs.chan_stats.offset == lib.mdx_offsetof_gemm_args_chan_stats()
-    assert _lib.GemmArgs._fields_[-1][0] == "chan_stats"
+    assert _lib.GemmArgs._fields_[-1][0] == "stride"
     # the documented stub declares the same fields in the same order
     doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
     stub = doc[doc.index("class GemmArgs"):doc.index("lib.mdx_gemm_tc.restype")]

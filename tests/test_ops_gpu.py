@@ -83,6 +83,35 @@ def test_gemm_tc_conv3x3(n, H, W, Cin, Cout):
     assert rel_err(out.view(n, H, W, Cout), ref) < 1e-2
 
 
+@pytest.mark.parametrize("n,H,W,Cin,Cout", [(2, 16, 16, 64, 128), (3, 64, 64, 64, 64), (2, 9, 12, 128, 64),
+                                            (130, 8, 8, 64, 64), (1, 32, 32, 320, 320)])
+def test_gemm_tc_conv3x3_stride2(n, H, W, Cin, Cout):
+    """Downsample (openaimodel.py:80-88: conv3x3, stride 2, pad 1) as strided TMA boxes: every tap is one box load over
+    every other input pixel, the halo zero-filled by TMA — against F.conv2d, even / odd sizes, fp32 trunk output with
+    the GroupNorm statistics of the result taken in the epilogue."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(n * H + Cin + Cout)
+    x = bf(torch.randn(n, H, W, Cin, generator=g))
+    w = bf(torch.randn(Cout, Cin, 3, 3, generator=g) / (9 * Cin) ** 0.5)
+    b = torch.randn(Cout, generator=g)
+    ref = conv_ref(x, w, b, stride=2)
+    OH, OW = ref.shape[1], ref.shape[2]
+    assert (OH, OW) == ((H - 1) // 2 + 1, (W - 1) // 2 + 1)
+    out = ops.gemm_tc([(x.cuda().bfloat16(), 9)], pack_k(w).cuda().bfloat16(), bias=b.cuda(), stride=2,
+                      out_dtype=torch.float32)
+    assert tuple(out.shape) == (n * OH * OW, Cout)
+    assert rel_err(out.view(n, OH, OW, Cout), ref) < 1e-4
+    slots = ops.stat_slots(n, OH, OW)
+    if slots:
+        chan = torch.full((n, slots, 2, Cout), float("nan"), device="cuda")
+        out2 = ops.gemm_tc([(x.cuda().bfloat16(), 9)], pack_k(w).cuda().bfloat16(), bias=b.cuda(), stride=2,
+                           out_dtype=torch.float32, chan_stats=chan)
+        assert torch.equal(out2, out)
+        sums = chan.sum(dim=1).cpu()                      # [n, 2, Cout]
+        assert torch.allclose(sums[:, 0], ref.sum(dim=(1, 2)), rtol=1e-3, atol=1e-2)
+        assert torch.allclose(sums[:, 1], (ref * ref).sum(dim=(1, 2)), rtol=1e-3, atol=1e-2)
+
+
 def test_gemm_tc_conv_with_fused_skip():
     """ResBlock tail: conv3x3(h) + conv1x1(concat(x1, x2)) accumulated in one TMEM tile (K-concatenation)."""
     ops = _ops()
