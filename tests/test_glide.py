@@ -4,7 +4,8 @@ guided ancestral sampling with learned sigma, and the DDIM upsampler.
 CPU tier: the oracle (oracle/glide.py) and the host-side schedule code against golden vectors from the executed
 reference (tests/golden/make_golden_glide.py).  GPU tier: the CUDA path against the same goldens.
 Tolerances: fp32 check mode 1e-4 of the output range per network evaluation (north star), 5e-4 after the chained
-loops; bf16 2e-2 of the range per evaluation and cosine >= 0.999 on the loop results (north star: final latents)."""
+loops; bf16 1e-2 of the range per network evaluation (the north star's eps bound; SRGAN, which is not a UNet, 2e-2)
+and cosine >= 0.999 on the loop results (north star: final latents)."""
 import os
 
 import numpy as np
@@ -115,7 +116,7 @@ def test_head_permutation_is_the_reference_split():
 # ------------------------------------------------------------------------------------------------------------
 # GPU tier
 # ------------------------------------------------------------------------------------------------------------
-MODES = [(torch.float32, 1e-4, 5e-4), (torch.bfloat16, 2e-2, None)]
+MODES = [(torch.float32, 1e-4, 5e-4), (torch.bfloat16, 1e-2, None)]
 
 
 @pytest.mark.gpu
@@ -280,8 +281,8 @@ def test_cuda_glide_shipped_architectures_bf16():
             ref = og.unet_forward(P, opts, x, t, tok, mask, low_res=lr)
             out = glide.create_upsample_model(P, **opts)(x.cuda(), t.cuda(), lr.cuda(), tok.cuda(), mask.cuda())
         assert tuple(out.shape) == tuple(ref.shape)
-        parity_log("glide shipped %d bf16" % size, rel(out, ref), 2e-2)
-        assert rel(out, ref) < 2e-2, (size, rel(out, ref))
+        parity_log("glide shipped %d bf16" % size, rel(out, ref), 1e-2)
+        assert rel(out, ref) < 1e-2, (size, rel(out, ref))
 
 
 # ------------------------------------------------------------------------------------------------------------
