@@ -371,6 +371,315 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Multi-item form of attn_tc_kernel: a CTA walks `ipc` consecutive (query tile, head, batch) work items
+// w = blockIdx.x * ipc + 0 .. ipc-1 (a handful; the grid stays several waves long so that the hardware's dynamic block
+// scheduling still evens out SM-to-SM differences — a fully static one-CTA-per-SM split measured slower on long
+// sequences).  With one 128-query tile per launch slot, a CTA's fill (TMEM allocation, barrier
+// set-up, the first Q / K loads' DRAM latency, the first score MMA) and drain (merge of the two softmax streams, the
+// output store) were exposed for every tile — about a tenth of a 32-key-tile item and a third of an 8-key-tile one.
+// Here the pipeline simply runs on: the K / V rings, the three score accumulators and all barriers keep one running
+// tile count across items, Q is double-buffered, so the producer is already fetching the next item's Q / K / V and
+// the MMA thread already issuing its first score tiles while the softmax warps finish and merge the current one.
+// Extra hand-offs: q_empty (the item's last score MMA has retired: its Q buffer may be refilled), o_empty[g] (group g
+// has read its finished output accumulator: the next item's first P V may overwrite it), and named barrier 2
+// (group 0 is done reading group 1's parked rows of the previous item).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int ATP_OFF_Q = 0;                                   // two Q buffers
+constexpr int ATP_OFF_K = ATP_OFF_Q + 2 * TILE_BYTES;
+constexpr int ATP_OFF_V = ATP_OFF_K + AT_KS * TILE_BYTES;
+constexpr int ATP_OFF_XCH = ATP_OFF_V + AT_VS * TILE_BYTES;
+constexpr int ATP_OFF_BAR = ATP_OFF_XCH + 2 * TILE_BYTES;
+constexpr int ATP_OFF_XML = ATP_OFF_BAR + 512;
+constexpr int ATP_SMEM = ATP_OFF_XML + 1024 + 1024;
+
+struct AttnTcPP {
+  AttnTcP a;
+  int nqt, heads, total;   // query tiles per (batch, head), heads, work items
+  int ipc;                 // work items per CTA (the last CTAs may get fewer)
+  int w_mul, w_stride;     // item wi of CTA c is w = c * w_mul + wi * w_stride: (ipc, 1) = consecutive items per CTA,
+                           // (1, gridDim.x) = one CTA per SM striding over all items
+};
+
+__global__ void __launch_bounds__(384, 1)
+attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                          const __grid_constant__ CUtensorMap tmV, const AttnTcPP pp) {
+  const AttnTcP& p = pp.a;
+  extern __shared__ uint8_t at_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ATP_OFF_BAR);
+  uint64_t* q_full = bars;                 // 2
+  uint64_t* q_empty = q_full + 2;          // 2
+  uint64_t* k_full = q_empty + 2;          // AT_KS
+  uint64_t* k_empty = k_full + AT_KS;      // AT_KS
+  uint64_t* v_full = k_empty + AT_KS;      // AT_VS
+  uint64_t* v_empty = v_full + AT_VS;      // AT_VS
+  uint64_t* s_full = v_empty + AT_VS;      // AT_SS
+  uint64_t* p_full = s_full + AT_SS;       // AT_SS
+  uint64_t* o_full = p_full + AT_SS;       // 2
+  uint64_t* o_empty = o_full + 2;          // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int T = (p.Nk + AT_BN - 1) / AT_BN;
+  const int w_first = (int)blockIdx.x * pp.w_mul;
+  int n_items = (pp.total - w_first + pp.w_stride - 1) / pp.w_stride;                  // work items of this CTA (>= 1)
+  n_items = n_items < pp.ipc ? n_items : pp.ipc;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+    for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
+    for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t TM_S = tmem_base;
+  const uint32_t TM_O = tmem_base + AT_SS * AT_BN;
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (warp == 0) {
+      if (elect_one()) {
+        // ===================== TMA producer: runs ahead across work items =====================
+        uint32_t jj = 0;                                    // running key-tile count
+        for (int wi = 0; wi < n_items; ++wi) {
+          const int w = w_first + wi * pp.w_stride;
+          const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
+          const int qs = wi & 1;
+          mbar_wait(&q_empty[qs], ((wi >> 1) & 1) ^ 1);
+          mbar_arrive_expect_tx(&q_full[qs], TILE_BYTES);
+          tma_load_4d(smem + ATP_OFF_Q + qs * TILE_BYTES, &tmQ, &q_full[qs], 0, head, qt * AT_BM, b);
+          for (int j = 0; j < T; ++j, ++jj) {
+            const int ks = jj % AT_KS, vs = jj % AT_VS;
+            mbar_wait(&k_empty[ks], ((jj / AT_KS) & 1) ^ 1);
+            mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
+            tma_load_4d(smem + ATP_OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], 0, head, j * AT_BN, b);
+            mbar_wait(&v_empty[vs], ((jj / AT_VS) & 1) ^ 1);
+            mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+            tma_load_4d(smem + ATP_OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        // ===================== MMA issuer: one flat sequence of key tiles over all items =====================
+        constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+        constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+        const uint32_t total_tiles = (uint32_t)n_items * (uint32_t)T;
+        // P V of running tile i (item i / T, tile i % T of it; group = that tile's parity inside the item)
+        auto issue_pv = [&](uint32_t i) {
+          const uint32_t wi = i / (uint32_t)T, wj = i - wi * (uint32_t)T;
+          const int pb = i % AT_SS, vs = i % AT_VS, ob = wj & 1;
+          if (wj < 2 && wi >= 1) {            // first P V of this group in a new item overwrites O[ob]:
+            mbar_wait(&o_empty[ob], (wi - 1) & 1);   // the group has read the previous item's result out of it
+          }
+          mbar_wait(&p_full[pb], (i / AT_SS) & 1);
+          mbar_wait(&v_full[vs], (i / AT_VS) & 1);
+          tc_fence_after();
+          const uint32_t p_tmem = TM_S + pb * AT_BN;
+          const uint32_t v_base = smem_u32(smem + ATP_OFF_V + vs * TILE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < AT_BN / 16; ++kk) {
+            umma_bf16_ts(TM_O + ob * AT_D, p_tmem + kk * 8, umma_desc_sw128_mn(v_base + kk * 16 * 128), idesc_o,
+                         (wj >= 2 || kk != 0) ? 1u : 0u);
+          }
+          umma_commit(&o_full[ob]);
+          umma_commit(&v_empty[vs]);
+        };
+        uint32_t wi = 0, j = 0;
+        for (uint32_t jj = 0; jj < total_tiles; ++jj) {
+          const int ks = jj % AT_KS, sb = jj % AT_SS, qs = wi & 1;
+          if (j == 0) mbar_wait(&q_full[qs], (wi >> 1) & 1);
+          mbar_wait(&k_full[ks], (jj / AT_KS) & 1);
+          tc_fence_after();
+          const uint32_t q_base = smem_u32(smem + ATP_OFF_Q + qs * TILE_BYTES);
+          const uint32_t k_base = smem_u32(smem + ATP_OFF_K + ks * TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < AT_D / 16; ++k)
+            umma_bf16(TM_S + sb * AT_BN, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s,
+                      k != 0 ? 1u : 0u);
+          umma_commit(&s_full[sb]);
+          umma_commit(&k_empty[ks]);
+          if (j == (uint32_t)T - 1) umma_commit(&q_empty[qs]);   // the item's score MMAs are all issued
+          if (jj >= 2) issue_pv(jj - 2);
+          if (++j == (uint32_t)T) { j = 0; ++wi; }
+        }
+        if (total_tiles >= 2) issue_pv(total_tiles - 2);
+        issue_pv(total_tiles - 1);
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    // ===================== softmax + output (as attn_tc_kernel, phases from running counts) =====================
+    const int g = (warp - 4) >> 2;
+    const int qw = warp & 3;
+    const int row = qw * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(qw * 32) << 16;
+    const float c = p.sl2;
+    const uint32_t to = TM_O + lane_off + g * AT_D;
+    float* xch = reinterpret_cast<float*>(smem + ATP_OFF_XCH);
+    float* xml = reinterpret_cast<float*>(smem + ATP_OFF_XML);
+    uint32_t pvc = 0;                                        // P V completions of this group waited for so far
+    for (int wi = 0; wi < n_items; ++wi) {
+      const int w = w_first + wi * pp.w_stride;
+      const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
+      const int q0 = qt * AT_BM;
+      float m_run = -INFINITY, l_run = 0.f;
+      int it = 0;
+      for (int j = g; j < T; j += 2, ++it) {
+        const uint32_t jj = (uint32_t)wi * (uint32_t)T + (uint32_t)j;
+        const int sb = jj % AT_SS;
+        mbar_wait(&s_full[sb], (jj / AT_SS) & 1);
+        tc_fence_after();
+        const uint32_t ts = TM_S + lane_off + sb * AT_BN;
+        const int key0 = j * AT_BN;
+        uint32_t sr[AT_BN];
+#pragma unroll
+        for (int cc = 0; cc < AT_BN / 32; ++cc) tmem_ld32(ts + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
+        tmem_ld_wait();
+        if (key0 + AT_BN > p.Nk) {
+#pragma unroll
+          for (int i = 0; i < AT_BN; ++i)
+            if (key0 + i >= p.Nk) sr[i] = 0xff800000u;
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < AT_BN; i += 8) {
+          mx0 = max3f(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+          mx1 = max3f(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+          mx2 = max3f(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
+          mx3 = max3f(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+        float alpha = 1.f;
+        const bool moved = (mx - m_run) * c > 8.f;
+        if (moved) {
+          alpha = ex2_approx((m_run - mx) * c);
+          l_run *= alpha;
+          m_run = mx;
+        }
+        if (it >= 1) {
+          mbar_wait(&o_full[g], pvc & 1);
+          ++pvc;
+          if (__any_sync(0xffffffffu, moved)) {
+            tc_fence_after();
+#pragma unroll
+            for (int cc = 0; cc < AT_D / 32; ++cc) {
+              uint32_t r[32];
+              tmem_ld32(to + cc * 32, r);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                float a0 = __uint_as_float(r[i]), a1 = __uint_as_float(r[i + 1]);
+                fmul2(a0, a1, alpha);
+                r[i] = __float_as_uint(a0);
+                r[i + 1] = __float_as_uint(a1);
+              }
+              tmem_st32(to + cc * 32, r);
+            }
+            tmem_st_wait();
+          }
+        }
+        float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const float nmsc = -m_run * c;
+        uint32_t pk[AT_BN / 2];
+#pragma unroll
+        for (int ch = 0; ch < AT_BN / 8; ++ch) {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int i = ch * 8 + h * 2;
+            float x0, x1;
+            ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
+            const float p0 = ex2_approx(x0);
+            const float p1 = ex2_approx(x1);
+            fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
+            pk[i >> 1] = pack_bf16x2(p0, p1);
+          }
+        }
+        tmem_st32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+        tmem_st32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+        tmem_st_wait();
+        l_run += ((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7]));
+        tc_fence_before();
+        mbar_arrive(&p_full[sb]);
+      }
+      // ---- this group's output row of the item, then hand O[g] back to the MMA thread ----
+      float o_acc[AT_D];
+#pragma unroll
+      for (int i = 0; i < AT_D; ++i) o_acc[i] = 0.f;
+      if (it >= 1) {
+        mbar_wait(&o_full[g], pvc & 1);
+        ++pvc;
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < AT_D / 32; ++cc) {
+          uint32_t r[32];
+          tmem_ld32(to + cc * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o_acc[cc * 32 + i] = __uint_as_float(r[i]);
+        }
+        tc_fence_before();
+      }
+      mbar_arrive(&o_empty[g]);
+      // ---- merge: group 1 parks (m, l, O), group 0 combines and stores ----
+      if (g == 1) {
+        if (wi >= 1) asm volatile("bar.sync 2, 256;" ::: "memory");   // group 0 has read the previous item's rows
+#pragma unroll
+        for (int i = 0; i < AT_D; ++i) xch[i * AT_BM + row] = o_acc[i];
+        xml[row * 2] = m_run;
+        xml[row * 2 + 1] = l_run;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (g == 0) {
+        const float m1 = xml[row * 2], l1 = xml[row * 2 + 1];
+        const float m = fmaxf(m_run, m1);
+        const float w0 = ex2_approx((m_run - m) * c);
+        const float w1 = (m1 == -INFINITY) ? 0.f : ex2_approx((m1 - m) * c);
+        const float inv = 1.f / (l_run * w0 + l1 * w1);
+        float f[AT_D];
+#pragma unroll
+        for (int i = 0; i < AT_D; ++i) f[i] = (o_acc[i] * w0 + xch[i * AT_BM + row] * w1) * inv;
+        if (wi + 1 < n_items) asm volatile("bar.arrive 2, 256;" ::: "memory");   // the parked rows may be overwritten
+        if (q0 + row < p.Nq) {
+          bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * p.d;
+#pragma unroll
+          for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+            if (v8 * 8 >= p.d) break;
+            uint4 u;
+            u.x = pack_bf16x2(f[v8 * 8], f[v8 * 8 + 1]);
+            u.y = pack_bf16x2(f[v8 * 8 + 2], f[v8 * 8 + 3]);
+            u.z = pack_bf16x2(f[v8 * 8 + 4], f[v8 * 8 + 5]);
+            u.w = pack_bf16x2(f[v8 * 8 + 6], f[v8 * 8 + 7]);
+            *reinterpret_cast<uint4*>(orow + v8 * 8) = u;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Single-tile variant: Nk <= 128 (the cross-attention over 77 text tokens, attention.py:118-152).  There is no
 // key loop to pipeline, so the CTA is small (4 role warps + ONE softmax warpgroup, 48 KiB smem, 128 TMEM columns:
 // S, then P over its first half and O over its second) and two CTAs share an SM to overlap each other's
@@ -576,16 +885,44 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
   if (attr.need()) {
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT1_SMEM));
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATP_SMEM));
     attr.mark();
   }
   AttnTcP p;
   p.Nq = Nq; p.Nk = Nk; p.sl2 = scale * 1.4426950408889634f;
   p.o = reinterpret_cast<bf16*>(o); p.ldo = ldo; p.d = d;
   dim3 grid((Nq + AT_BM - 1) / AT_BM, heads, batch);
-  if (Nk <= AT_BN && !getenv("MDX_ATTN_NO_SINGLE"))
+  // Launch form.  Measured in one process (tools/attn_ab.py, CFG batch 128): one CTA per SM striding over all query
+  // tiles beats one tile per CTA by 3 % at 4096 keys, 13 % at 1024 and 26 % at 256 (a CTA's fill and drain are
+  // overlapped with the neighbouring tiles), but loses 4-9 % on long sequences (9216 keys) and when an SM gets fewer
+  // than ~30 tiles; a few consecutive tiles per CTA sits in between.  MDX_ATTN_NO_PERSIST / MDX_ATTN_IPC force a form.
+  const bool no_persist = getenv("MDX_ATTN_NO_PERSIST") != nullptr;
+  const char* ipc_s = getenv("MDX_ATTN_IPC");                 // items per CTA, 0 = one CTA per SM
+  const int ipc_env = ipc_s ? atoi(ipc_s) : -1;
+  const int sms = mdx_num_sms();
+  const long long total = (long long)grid.x * heads * batch;
+  const int T = (Nk + AT_BN - 1) / AT_BN;
+  const bool persist = ipc_env >= 0 || (!no_persist && T <= 32 && total >= 32ll * sms);
+  if (Nk <= AT_BN && !getenv("MDX_ATTN_NO_SINGLE")) {
     attn_tc_single_kernel<<<grid, 256, AT1_SMEM, st>>>(mq, mk, mv, p);
-  else
+  } else if (!persist) {
     attn_tc_kernel<<<grid, 384, AT_SMEM, st>>>(mq, mk, mv, p);
+  } else {
+    AttnTcPP pp;
+    pp.a = p;
+    pp.nqt = (int)grid.x; pp.heads = heads;
+    MDX_CHECK_ARG(total < (1ll << 31), "mdx_attention: too many query tiles");
+    pp.total = (int)total;
+    if (ipc_env <= 0) {
+      const unsigned g = (unsigned)(total < sms ? total : sms);
+      pp.ipc = (int)((total + g - 1) / g); pp.w_mul = 1; pp.w_stride = (int)g;
+      attn_tc_persistent_kernel<<<g, 384, ATP_SMEM, st>>>(mq, mk, mv, pp);
+    } else {
+      const long long ipc = ipc_env > 8 ? 8 : ipc_env;
+      pp.ipc = (int)ipc; pp.w_mul = (int)ipc; pp.w_stride = 1;
+      attn_tc_persistent_kernel<<<(unsigned)((total + ipc - 1) / ipc), 384, ATP_SMEM, st>>>(mq, mk, mv, pp);
+    }
+  }
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;
