@@ -829,6 +829,211 @@ attn_tc_single_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Multi-item form of the single-tile case (Nk <= 128: the cross-attention over 77 text tokens).  One item = one
+// 128-query tile against one key tile: a score MMA, one softmax, one P V — a pure latency chain when every item is its
+// own CTA.  Here a CTA (one per SM) walks its items and the two softmax warpgroups take ALTERNATE items (group g owns
+// items g, g+2, ... with O[g] and no merge), so one group's exponentials run while the other waits for its P V, the
+// MMA thread issues score MMAs two items ahead, and the producer keeps three items' K / V and two items' Q in flight.
+// Only the key columns that exist are loaded, exponentiated and multiplied (77 keys: 3 of 4 score column groups, 10
+// of 16 exp chunks, 5 of 8 P V steps).
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(384, 1)
+attn_tc_single_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                                 const __grid_constant__ CUtensorMap tmV, const AttnTcPP pp) {
+  const AttnTcP& p = pp.a;
+  extern __shared__ uint8_t at_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(at_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ATP_OFF_BAR);
+  uint64_t* q_full = bars;                 // 2
+  uint64_t* q_empty = q_full + 2;          // 2
+  uint64_t* k_full = q_empty + 2;          // AT_KS
+  uint64_t* k_empty = k_full + AT_KS;      // AT_KS
+  uint64_t* v_full = k_empty + AT_KS;      // AT_VS
+  uint64_t* v_empty = v_full + AT_VS;      // AT_VS
+  uint64_t* s_full = v_empty + AT_VS;      // AT_SS
+  uint64_t* p_full = s_full + AT_SS;       // AT_SS
+  uint64_t* o_full = p_full + AT_SS;       // 2
+  uint64_t* o_empty = o_full + 2;          // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = (int)gridDim.x;
+  const int n_items = (pp.total - (int)blockIdx.x + G - 1) / G;     // items w = blockIdx.x + wi * G of this CTA (>= 1)
+  const int ksteps = (p.Nk + 15) / 16;                              // P V only over the 16-key blocks that hold keys
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+    for (int i = 0; i < AT_KS; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
+    for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t TM_S = tmem_base;
+  const uint32_t TM_O = tmem_base + AT_SS * AT_BN;
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (warp == 0) {
+      if (elect_one()) {
+        for (int wi = 0; wi < n_items; ++wi) {
+          const int w = (int)blockIdx.x + wi * G;
+          const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
+          const int qs = wi & 1, ks = wi % AT_KS, vs = wi % AT_VS;
+          mbar_wait(&q_empty[qs], ((wi >> 1) & 1) ^ 1);
+          mbar_arrive_expect_tx(&q_full[qs], TILE_BYTES);
+          tma_load_4d(smem + ATP_OFF_Q + qs * TILE_BYTES, &tmQ, &q_full[qs], 0, head, qt * AT_BM, b);
+          mbar_wait(&k_empty[ks], ((wi / AT_KS) & 1) ^ 1);
+          mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
+          tma_load_4d(smem + ATP_OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], 0, head, 0, b);
+          mbar_wait(&v_empty[vs], ((wi / AT_VS) & 1) ^ 1);
+          mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+          tma_load_4d(smem + ATP_OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, 0, b);
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+        constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+        auto issue_pv = [&](int i) {
+          const int pb = i % AT_SS, vs = i % AT_VS, ob = i & 1;
+          if (i >= 2) mbar_wait(&o_empty[ob], ((i >> 1) - 1) & 1);   // the group has read item i-2's result out of O[ob]
+          mbar_wait(&p_full[pb], (i / AT_SS) & 1);
+          mbar_wait(&v_full[vs], (i / AT_VS) & 1);
+          tc_fence_after();
+          const uint32_t p_tmem = TM_S + pb * AT_BN;
+          const uint32_t v_base = smem_u32(smem + ATP_OFF_V + vs * TILE_BYTES);
+          for (int kk = 0; kk < ksteps; ++kk)
+            umma_bf16_ts(TM_O + ob * AT_D, p_tmem + kk * 8, umma_desc_sw128_mn(v_base + kk * 16 * 128), idesc_o,
+                         kk != 0 ? 1u : 0u);
+          umma_commit(&o_full[ob]);
+          umma_commit(&v_empty[vs]);
+        };
+        for (int wi = 0; wi < n_items; ++wi) {
+          const int ks = wi % AT_KS, sb = wi % AT_SS, qs = wi & 1;
+          mbar_wait(&q_full[qs], (wi >> 1) & 1);
+          mbar_wait(&k_full[ks], (wi / AT_KS) & 1);
+          tc_fence_after();
+          const uint32_t q_base = smem_u32(smem + ATP_OFF_Q + qs * TILE_BYTES);
+          const uint32_t k_base = smem_u32(smem + ATP_OFF_K + ks * TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < AT_D / 16; ++k)
+            umma_bf16(TM_S + sb * AT_BN, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s,
+                      k != 0 ? 1u : 0u);
+          umma_commit(&s_full[sb]);
+          umma_commit(&k_empty[ks]);
+          umma_commit(&q_empty[qs]);
+          if (wi >= 2) issue_pv(wi - 2);
+        }
+        if (n_items >= 2) issue_pv(n_items - 2);
+        issue_pv(n_items - 1);
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    const int g = (warp - 4) >> 2;
+    const int qw = warp & 3;
+    const int row = qw * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(qw * 32) << 16;
+    const float c = p.sl2;
+    const uint32_t to = TM_O + lane_off + g * AT_D;
+    for (int wi = g; wi < n_items; wi += 2) {
+      const int w = (int)blockIdx.x + wi * G;
+      const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
+      const int q0 = qt * AT_BM;
+      const int sb = wi % AT_SS;
+      mbar_wait(&s_full[sb], (wi / AT_SS) & 1);
+      tc_fence_after();
+      const uint32_t ts = TM_S + lane_off + sb * AT_BN;
+      uint32_t sr[AT_BN];
+#pragma unroll
+      for (int cc = 0; cc < AT_BN / 32; ++cc)
+        if (cc * 32 < p.Nk) tmem_ld32(ts + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < AT_BN; ++i)
+        if (i >= p.Nk) sr[i] = 0xff800000u;            // keys beyond Nk (and the column groups not loaded): -inf
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < AT_BN; i += 8) {
+        mx0 = max3f(mx0, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]));
+        mx1 = max3f(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+        mx2 = max3f(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
+        mx3 = max3f(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
+      }
+      const float nmsc = -fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * c;
+      float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      uint32_t pk[AT_BN / 2];
+#pragma unroll
+      for (int ch = 0; ch < AT_BN / 8; ++ch) {
+        if (ch * 8 < p.Nk) {                            // warp-uniform: chunks with no real key are skipped
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const int i = ch * 8 + h * 2;
+            float x0, x1;
+            ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
+            const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+            fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
+            pk[i >> 1] = pack_bf16x2(p0, p1);
+          }
+        } else {
+#pragma unroll
+          for (int h = 0; h < 4; ++h) pk[(ch * 8 + h * 2) >> 1] = 0u;
+        }
+      }
+      const float l = ((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7]));
+      tmem_st32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+      tmem_st32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&p_full[sb]);
+      const float inv = 1.f / l;
+      mbar_wait(&o_full[g], (wi >> 1) & 1);
+      tc_fence_after();
+      uint32_t r[AT_D];
+      tmem_ld32(to, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+      tmem_ld32(to + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&o_empty[g]);
+      if (q0 + row < p.Nq) {
+        bf16* orow = p.o + ((long long)b * p.Nq + q0 + row) * p.ldo + head * p.d;
+#pragma unroll
+        for (int v8 = 0; v8 < AT_D / 8; ++v8) {
+          if (v8 * 8 >= p.d) break;
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(r[v8 * 8]) * inv, __uint_as_float(r[v8 * 8 + 1]) * inv);
+          u.y = pack_bf16x2(__uint_as_float(r[v8 * 8 + 2]) * inv, __uint_as_float(r[v8 * 8 + 3]) * inv);
+          u.z = pack_bf16x2(__uint_as_float(r[v8 * 8 + 4]) * inv, __uint_as_float(r[v8 * 8 + 5]) * inv);
+          u.w = pack_bf16x2(__uint_as_float(r[v8 * 8 + 6]) * inv, __uint_as_float(r[v8 * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + v8 * 8) = u;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -886,6 +1091,8 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT1_SMEM));
     MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATP_SMEM));
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_single_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        ATP_SMEM));
     attr.mark();
   }
   AttnTcP p;
@@ -904,7 +1111,17 @@ int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long 
   const int T = (Nk + AT_BN - 1) / AT_BN;
   const bool persist = ipc_env >= 0 || (!no_persist && T <= 32 && total >= 32ll * sms);
   if (Nk <= AT_BN && !getenv("MDX_ATTN_NO_SINGLE")) {
-    attn_tc_single_kernel<<<grid, 256, AT1_SMEM, st>>>(mq, mk, mv, p);
+    // single key tile (cross-attention): with enough items per SM the multi-item kernel pipelines them
+    if (!no_persist && total >= 8ll * sms) {
+      AttnTcPP pp;
+      pp.a = p;
+      pp.nqt = (int)grid.x; pp.heads = heads;
+      MDX_CHECK_ARG(total < (1ll << 31), "mdx_attention: too many query tiles");
+      pp.total = (int)total; pp.ipc = 0; pp.w_mul = 1; pp.w_stride = sms;
+      attn_tc_single_persistent_kernel<<<sms, 384, ATP_SMEM, st>>>(mq, mk, mv, pp);
+    } else {
+      attn_tc_single_kernel<<<grid, 256, AT1_SMEM, st>>>(mq, mk, mv, p);
+    }
   } else if (!persist) {
     attn_tc_kernel<<<grid, 384, AT_SMEM, st>>>(mq, mk, mv, p);
   } else {
