@@ -29,6 +29,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+PAIR_TIMEOUT = 240   # seconds the CFG pair-split phase (N >= 2) may take before every rank gives up on it
 FLOP_PER_SAMPLE_FWD_SD2_64 = 804.3e9  # SURVEY.md §3.4 / BASELINE.md §3 (2*MAC), per sample per UNet forward
 
 SD2_UNET = dict(in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],
@@ -321,12 +322,88 @@ def run_b200(a):
     value = images / (ms / 1e3)
     e2e = images / (ms_e2e / 1e3)
 
+    # ---- dominant kernel, live: every mdx_gemm_tc launch of one guided UNet evaluation ----
+    prof = []
+    ops.GEMM_TC_PROFILE = prof
+    unet.use_cuda_graph = False
+    rep = 1 if a.cfg_split else 2
+    t_probe = torch.full((rep * B,), 501.0, device=dev)
+    if rep == 2:
+        unet.set_context(torch.cat((uc_dev, c_dev), 0))   # the pair-split phase left a single-branch context behind
+    unet.forward_nhwc(x_dev, t_probe, repeat=rep)
+    torch.cuda.synchronize()
+    ops.GEMM_TC_PROFILE = None
+    flops = sum(p_[0] for p_ in prof)
+    gemm_ms = sum(p_[1].elapsed_time(p_[2]) for p_ in prof)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    peak_burst = float(peaks.get("bf16_tflops", 1650.0))
+    hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
+    peak_kind = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md, sustained)"
+    achieved = flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
+    hbm_kernels = hbm_probe(torch, ops, dev, B, h, hbm_peak) if world == 1 else None
+    fwd_flops = FLOP_PER_SAMPLE_FWD_SD2_64 * (h / 64.0) ** 2  # conv/linear scale ~ pixels; attention differs slightly
+    step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None  # per GPU
+
+    # ---- the line as measured so far (rank 0); the pair-split phase below can only add to it ----
+    base_line = None
+    if rank == 0:
+        cpu = None
+        if not a.no_cpu_baseline and world == 1:
+            times, cores = cpu_sample_seconds(a, 1)
+            cpu = {"value": 1.0 / (S * times[0]), "unit": "images/s", "cores": cores, "kind": "port",
+                   "sample": "one CFG UNet evaluation (batch 2, %dx%d latent) + DDIM update for 1 image = 1 of %d steps, "
+                             "extrapolated x%d; oracle (torch fp32 restatement), MindSpore not installable" % (h, h, S, S)}
+
+        base_line = {
+            "metric": "images/sec @512^2 50-step DDIM CFG7.5", "value": value, "unit": "images/s", "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(a), "global_batch": B * groups, "sampler": "DDIM", "sampler_steps": S,
+                       "cfg_scale": a.scale, "parallelism": ("dp%d x cfg-pair-split (per-step 2-rank eps all-gather over NCCL)" % groups) if a.cfg_split
+                       else "dp%d (independent prompt batches, no collective)" % world,
+                       "l2": "inputs larger than L2 (weights 1.7 GB + activations >> 126 MB)",
+                       "cuda_graph": not a.no_graph},
+            "clocks": clk,
+            "e2e": {"value": e2e, "unit": "images/s",
+                    "h2d_bytes_per_step": (x_host.numel() + c_host.numel() + uc_host.numel()) * 4,
+                    "d2h_bytes_per_step": out_host.numel() * 4},
+            "gpu_launches": int(launches),
+            "unet_eval_ms": ms / a.steps / S,
+            "unet_tflops_per_gpu": step_tflops,
+            "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (mdx_gemm_tc: conv3x3 / 1x1 / dense)",
+                         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                         "peak_kind": peak_kind, "frac_of_burst_peak": achieved / peak_burst, "peak_burst": peak_burst,
+                         "traffic": TRAFFIC["bytes_per_launch"], "traffic_note": TRAFFIC["note"],
+                         "launches": len(prof), "kernel_ms_per_unet_eval": gemm_ms,
+                         "whole_step_frac": (step_tflops / peak) if step_tflops else None,
+                         "whole_step_frac_of_burst_peak": (step_tflops / peak_burst) if step_tflops else None},
+            "hbm_kernels": hbm_kernels,
+            "cpu_baseline": cpu,
+        }
+
     # ---- N >= 2, same run: CFG pair split (BASELINE config #3).  GPU 2k evaluates the unconditional half of a batch
     #      of B prompts, GPU 2k+1 the conditional half; each step the 4-channel eps halves are exchanged with one NCCL
     #      all-gather issued INSIDE the captured step graph and both ranks apply the same update. ----
     pair = None
+    watchdog = None
     if world >= 2 and world % 2 == 0 and not a.cfg_split and not a.no_pair_split:
         from minddiffusion_b200.parallel import CfgPairSplit
+        # Everything above is measured; what follows adds collectives.  A rank that never comes back from one must not
+        # cost the run its line: after PAIR_TIMEOUT seconds every rank leaves, rank 0 printing the line it has.
+        def give_up():
+            if rank == 0:
+                base_line["pair_split"] = {"error": "pair-split phase did not finish within %d s" % PAIR_TIMEOUT}
+                print(json.dumps(base_line), flush=True)
+            os._exit(0)
+        watchdog = threading.Timer(PAIR_TIMEOUT, give_up)
+        watchdog.daemon = True
+        watchdog.start()
+        unet.use_cuda_graph = not a.no_graph
         ldm.cfg_split = split = CfgPairSplit()
         xp = torch.from_numpy(np.random.RandomState(42 + rank // 2).randn(B, *shape).astype(np.float32)).to(dev)
         step_pair = lambda: sampler.sample(S, B, shape, c_dev, x_T=xp, verbose=False, eta=0.0,
@@ -356,75 +433,12 @@ def run_b200(a):
                                % (world // 2, "captured inside the step graph" if split.in_graph
                                   else "issued between the two captured segments of a step")}
         ldm.cfg_split = None
+        watchdog.cancel()
 
-    # ---- dominant kernel, live: every mdx_gemm_tc launch of one guided UNet evaluation ----
-    prof = []
-    ops.GEMM_TC_PROFILE = prof
-    unet.use_cuda_graph = False
-    rep = 1 if a.cfg_split else 2
-    t_probe = torch.full((rep * B,), 501.0, device=dev)
-    if rep == 2:
-        unet.set_context(torch.cat((uc_dev, c_dev), 0))   # the pair-split phase left a single-branch context behind
-    unet.forward_nhwc(x_dev, t_probe, repeat=rep)
-    torch.cuda.synchronize()
-    ops.GEMM_TC_PROFILE = None
-    flops = sum(p_[0] for p_ in prof)
-    gemm_ms = sum(p_[1].elapsed_time(p_[2]) for p_ in prof)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except (OSError, ValueError):
-        pass
-    peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-    peak_burst = float(peaks.get("bf16_tflops", 1650.0))
-    hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
-    peak_kind = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md, sustained)"
-    achieved = flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
-    hbm_kernels = hbm_probe(torch, ops, dev, B, h, hbm_peak) if world == 1 else None
-    fwd_flops = FLOP_PER_SAMPLE_FWD_SD2_64 * (h / 64.0) ** 2  # conv/linear scale ~ pixels; attention differs slightly
-    step_tflops = value / world * S * 2 * FLOP_PER_SAMPLE_FWD_SD2_64 / 1e12 if h == 64 else None  # per GPU
-
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-
-    cpu = None
-    if not a.no_cpu_baseline and world == 1:
-        times, cores = cpu_sample_seconds(a, 1)
-        cpu = {"value": 1.0 / (S * times[0]), "unit": "images/s", "cores": cores, "kind": "port",
-               "sample": "one CFG UNet evaluation (batch 2, %dx%d latent) + DDIM update for 1 image = 1 of %d steps, "
-                         "extrapolated x%d; oracle (torch fp32 restatement), MindSpore not installable" % (h, h, S, S)}
-
-    line = {
-        "metric": "images/sec @512^2 50-step DDIM CFG7.5", "value": value, "unit": "images/s", "n_gpus": world,
-        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": workload_name(a), "global_batch": B * groups, "sampler": "DDIM", "sampler_steps": S,
-                   "cfg_scale": a.scale, "parallelism": ("dp%d x cfg-pair-split (per-step 2-rank eps all-gather over NCCL)" % groups) if a.cfg_split
-                   else "dp%d (independent prompt batches, no collective)" % world,
-                   "l2": "inputs larger than L2 (weights 1.7 GB + activations >> 126 MB)",
-                   "cuda_graph": not a.no_graph},
-        "clocks": clk,
-        "e2e": {"value": e2e, "unit": "images/s",
-                "h2d_bytes_per_step": (x_host.numel() + c_host.numel() + uc_host.numel()) * 4,
-                "d2h_bytes_per_step": out_host.numel() * 4},
-        "gpu_launches": int(launches),
-        "unet_eval_ms": ms / a.steps / S,
-        "unet_tflops_per_gpu": step_tflops,
-        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (mdx_gemm_tc: conv3x3 / 1x1 / dense)",
-                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-                     "peak_kind": peak_kind, "frac_of_burst_peak": achieved / peak_burst, "peak_burst": peak_burst,
-                     "traffic": TRAFFIC["bytes_per_launch"], "traffic_note": TRAFFIC["note"],
-                     "launches": len(prof), "kernel_ms_per_unet_eval": gemm_ms,
-                     "whole_step_frac": (step_tflops / peak) if step_tflops else None,
-                     "whole_step_frac_of_burst_peak": (step_tflops / peak_burst) if step_tflops else None},
-        "hbm_kernels": hbm_kernels,
-        "cpu_baseline": cpu,
-    }
-    if pair is not None:
-        line["pair_split"] = pair
-    print(json.dumps(line))
+    if rank == 0:
+        if pair is not None:
+            base_line["pair_split"] = pair
+        print(json.dumps(base_line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
