@@ -306,6 +306,52 @@ def test_attention_scores_growing_across_key_tiles(d, heads):
     assert rel_err(out, ref) < 2e-2
 
 
+@pytest.mark.parametrize("mode", ["one-cta-per-sm", "3-tiles-per-cta", "7-tiles-per-cta"])
+@pytest.mark.parametrize("B,heads,Nq,Nk,d", [(3, 5, 1000, 1000, 64), (2, 8, 700, 300, 40), (5, 2, 256, 2049, 64),
+                                             (40, 4, 128, 128 + 64, 64)])
+def test_attention_multi_item_launch_forms(monkeypatch, mode, B, heads, Nq, Nk, d):
+    """The multi-item (persistent) form of the tcgen05 attention kernel — K / V rings, score accumulators and barriers
+    running on across query tiles, Q double-buffered — which the launcher only picks on its own for large batches:
+    forced here in its three work splits, against the one-tile-per-CTA kernel (bit-identical) and the reference.
+    Covers ragged last key tiles, a single query tile per head, odd numbers of key tiles (the two softmax groups
+    then swap roles between items) and CTAs whose last items are missing."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(B * heads + Nq + Nk)
+    C = heads * d
+    q = bf(torch.randn(B, Nq, C, generator=g))
+    k = bf(torch.randn(B, Nk, C, generator=g))
+    v = bf(torch.randn(B, Nk, C, generator=g))
+    scale = d ** -0.5
+    ref = attn_ref(q, k, v, heads, scale)
+    qd, kd, vd = (t.cuda().to(torch.bfloat16) for t in (q, k, v))
+    monkeypatch.setenv("MDX_ATTN_NO_PERSIST", "1")
+    base = ops.attention(qd, kd, vd, heads, scale)
+    monkeypatch.delenv("MDX_ATTN_NO_PERSIST")
+    monkeypatch.setenv("MDX_ATTN_IPC", {"one-cta-per-sm": "0", "3-tiles-per-cta": "3", "7-tiles-per-cta": "7"}[mode])
+    out = ops.attention(qd, kd, vd, heads, scale)
+    assert torch.equal(out, base)
+    assert rel_err(out, ref) < 2e-2
+
+
+@pytest.mark.parametrize("B,heads,Nq,Nk,d", [(16, 10, 1024, 77, 64), (150, 8, 200, 128, 40), (1300, 1, 128, 1, 64)])
+def test_cross_attention_multi_item_kernel(monkeypatch, B, heads, Nq, Nk, d):
+    """One key tile (cross-attention over the text tokens) with many items per SM: the kernel in which the two softmax
+    warpgroups take alternate items — against the one-item-per-CTA kernel (bit-identical) and the reference."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(B + heads + Nq + Nk)
+    C = heads * d
+    q = bf(torch.randn(B, Nq, C, generator=g))
+    k = bf(torch.randn(B, Nk, C, generator=g))
+    v = bf(torch.randn(B, Nk, C, generator=g))
+    scale = d ** -0.5
+    qd, kd, vd = (t.cuda().to(torch.bfloat16) for t in (q, k, v))
+    out = ops.attention(qd, kd, vd, heads, scale)          # >= 8 items per SM: the multi-item kernel
+    monkeypatch.setenv("MDX_ATTN_NO_PERSIST", "1")
+    base = ops.attention(qd, kd, vd, heads, scale)
+    assert torch.equal(out, base)
+    assert rel_err(out, attn_ref(q, k, v, heads, scale)) < 2e-2
+
+
 # ------------------------------------------------------------------ movers and small kernels
 def test_timestep_embedding():
     import math

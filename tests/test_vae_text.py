@@ -2,7 +2,8 @@
 
 CPU tier: the oracle (oracle/vae_text.py) against golden vectors from the executed reference
 (tests/golden/make_golden2.py).  GPU tier: the CUDA path against the same goldens and against the oracle at a larger
-size; fp32 check mode 1e-4 (decoder: 2e-4, ten chained blocks), bf16 2e-2 of the output range."""
+size; fp32 check mode 1e-4 (decoder: 2e-4, ten chained blocks); bf16: text towers 1e-2, VAE decoder 2e-2 of the output
+range (measured 0.9e-2 on the small decoder, 1.2e-2 on the shipped shape: 23 chained conv blocks in bf16 storage)."""
 import os
 
 import numpy as np
@@ -59,7 +60,7 @@ def test_decoder_inventory():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("family", ["sd2", "wukong"])
-@pytest.mark.parametrize("dtype,tol_vae,tol_text", [(torch.float32, 2e-4, 1e-4), (torch.bfloat16, 2e-2, 2e-2)],
+@pytest.mark.parametrize("dtype,tol_vae,tol_text", [(torch.float32, 2e-4, 1e-4), (torch.bfloat16, 2e-2, 1e-2)],
                          ids=["fp32", "bf16"])
 def test_cuda_vae_and_text_against_goldens(family, dtype, tol_vae, tol_text):
     from minddiffusion_b200.autoencoder import AutoencoderKL, random_decoder_params
