@@ -93,6 +93,66 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// 2^x for a pair of lanes on the FMA pipe instead of the MUFU.  At d = 64 the 128 exponentials per score row take
+// twice the MUFU cycles the tile's two MMAs take on the tensor pipe, so a share of them is moved: floor(x) by a
+// round-down magic add, 2^frac by a degree-3 fit on [0, 1) (relative error 8.8e-5, well under P's bf16 rounding;
+// exact at frac = 0, so the row maximum still maps to 1), floor(x) added into the exponent field as an integer.
+#ifndef MDX_ATTN_POLY_NUM
+#define MDX_ATTN_POLY_NUM 3                                  // pairs out of every MDX_ATTN_POLY_DEN that take this path
+#endif
+#ifndef MDX_ATTN_POLY_DEN
+#define MDX_ATTN_POLY_DEN 16
+#endif
+__device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float x1) {
+  x0 = fmaxf(x0, -126.f);                                    // masked keys arrive as -inf; 2^-126 is zero to bf16 P
+  x1 = fmaxf(x1, -126.f);
+  uint32_t t0, t1, q0, q1;
+  asm("{\n\t.reg .b64 x, k, t, f, p, c;\n\t"
+      "mov.b64 x, {%4, %5};\n\t"
+      "mov.b64 k, {%6, %6};\n\t"
+      "add.rm.f32x2 t, x, k;\n\t"                            // low mantissa bits of t = floor(x)
+      "sub.rn.f32x2 f, t, k;\n\t"
+      "sub.rn.f32x2 f, x, f;\n\t"                            // frac in [0, 1)
+      "mov.b64 p, {%7, %7};\n\t"
+      "mov.b64 c, {%8, %8};\n\t"
+      "fma.rn.f32x2 p, p, f, c;\n\t"
+      "mov.b64 c, {%9, %9};\n\t"
+      "fma.rn.f32x2 p, p, f, c;\n\t"
+      "mov.b64 c, {%10, %10};\n\t"
+      "fma.rn.f32x2 p, p, f, c;\n\t"
+      "mov.b64 {%0, %1}, t;\n\t"
+      "mov.b64 {%2, %3}, p;\n\t}"
+      : "=r"(t0), "=r"(t1), "=r"(q0), "=r"(q1)
+      : "f"(x0), "f"(x1), "f"(12582912.f), "f"(0.077119089663028717041015625f), "f"(0.227564394474029541015625f),
+        "f"(0.695146143436431884765625f), "f"(1.f));
+  p0 = __uint_as_float(q0 + (t0 << 23));
+  p1 = __uint_as_float(q1 + (t1 << 23));
+}
+#ifdef MDX_ATTN_TRACE
+// debug build only: CTA 0 of the persistent kernel stamps (event, tile, clock) per role into a device array that
+// tools/attn_trace.py reads back through mdx_attn_trace_dump
+constexpr int AT_TR_N = 4096;                                // records per role
+__device__ uint32_t at_trace[4 * AT_TR_N * 2];
+#define AT_TR(role, ev, tile)                                                              \
+  do {                                                                                     \
+    if (blockIdx.x == 0 && tr_n < AT_TR_N) {                                               \
+      at_trace[((role) * AT_TR_N + tr_n) * 2] = ((uint32_t)(ev) << 24) | (uint32_t)(tile); \
+      at_trace[((role) * AT_TR_N + tr_n) * 2 + 1] = (uint32_t)clock();                     \
+      ++tr_n;                                                                              \
+    }                                                                                      \
+  } while (0)
+#else
+#define AT_TR(role, ev, tile) do { } while (0)
+#endif
+// exp2 of the pair with index k of a score row: the MUFU for most pairs, the FMA-pipe form for the chosen share
+__device__ __forceinline__ void ex2_pair(int k, float& p0, float& p1, float x0, float x1) {
+  if ((k % MDX_ATTN_POLY_DEN) < MDX_ATTN_POLY_NUM) {
+    ex2_poly2(p0, p1, x0, x1);
+  } else {
+    p0 = ex2_approx(x0);
+    p1 = ex2_approx(x1);
+  }
+}
 // MN-major operand (V as B of the P V product): rows of 64 elements (128 B) along N, 8-row swizzle atoms along K,
 // 1024 B between atoms (SBO).  Same bit layout as umma_desc_sw128; LBO is unused because N spans one atom.
 __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr) { return umma_desc_sw128(smem_addr); }
@@ -114,7 +174,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* p_full = s_full + AT_SS;       // AT_SS
   uint64_t* o_full = p_full + AT_SS;       // 2
   uint64_t* o_empty = o_full + 2;          // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+  uint64_t* s_empty = o_empty + 2;         // AT_SS: P V of the stage has completed, the next score MMA may overwrite it
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + AT_SS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * AT_BM;
@@ -132,6 +193,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
     for (int i = 0; i < 2; ++i) mbar_init(&o_full[i], 1);
+    for (int i = 0; i < AT_SS; ++i) mbar_init(&s_empty[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -152,64 +214,96 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  // Roles as in attn_tc_persistent_kernel (see the notes there): K and V each have their own producer thread, the
+  // score MMAs and the P V MMAs each their own issuing thread with s_empty carrying the one ordering the single
+  // issuer used to get from program order; both issue loops are unrolled by the ring depth so that stage and parity
+  // are immediates.
   if (warp == 0) {
     if (elect_one()) {
-      // ===================== TMA producer =====================
+      // ===================== TMA producer: Q, then the K tiles =====================
       mbar_arrive_expect_tx(q_full, TILE_BYTES);
       tma_load_4d(smem + OFF_Q, &tmQ, q_full, 0, head, q0, b);
+      uint32_t ks = 0, kph = 1;
       for (int j = 0; j < T; ++j) {
-        const int ks = j % AT_KS, vs = j % AT_VS;
-        mbar_wait(&k_empty[ks], ((j / AT_KS) & 1) ^ 1);
+        mbar_wait(&k_empty[ks], kph);
         mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
         tma_load_4d(smem + OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], 0, head, j * AT_BN, b);
-        mbar_wait(&v_empty[vs], ((j / AT_VS) & 1) ^ 1);
-        mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
-        tma_load_4d(smem + OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
+        if (++ks == AT_KS) { ks = 0; kph ^= 1; }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 3) {
     if (elect_one()) {
-      // ===================== MMA issuer =====================
-      constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
-      constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
-      const uint32_t q_base = smem_u32(smem + OFF_Q);
-      auto issue_pv = [&](int i) {
-        const int pb = i % AT_SS, vs = i % AT_VS, ob = i & 1;
-        mbar_wait(&p_full[pb], (i / AT_SS) & 1);
-        mbar_wait(&v_full[vs], (i / AT_VS) & 1);
-        tc_fence_after();
-        const uint32_t p_tmem = TM_S + pb * AT_BN;   // P_i (bf16 pairs, 64 columns) sits where S_i was
-        const uint32_t v_base = smem_u32(smem + OFF_V + vs * TILE_BYTES);
-#pragma unroll
-        for (int kk = 0; kk < AT_BN / 16; ++kk) {
-          const uint32_t b_addr = v_base + kk * 16 * 128;                          // 16 key rows of 128 B
-          // A = P from TMEM (16 keys = 8 columns of bf16 pairs).  O[ob] accumulates over all of the group's tiles;
-          // the softmax rescales it in place when its row max moves
-          umma_bf16_ts(TM_O + ob * AT_D, p_tmem + kk * 8, umma_desc_sw128_mn(b_addr), idesc_o,
-                       (i >= 2 || kk != 0) ? 1u : 0u);
-        }
-        umma_commit(&o_full[ob]);
-        umma_commit(&v_empty[vs]);
-      };
-      mbar_wait(q_full, 0);
-      // issue order S0 S1 S2 PV0 S3 PV1 ...: the scores of a group's next tile are complete before the group finishes
-      // its current one.  S_j reuses the TMEM buffer of S_{j-3} / P_{j-3}; P V_{j-3} was issued (after waiting for
-      // P_{j-3}) earlier in this thread's program order and tcgen05.mma executes in issue order, so no barrier is needed
+      // ===================== TMA producer: the V tiles =====================
+      uint32_t vs = 0, vph = 1;
       for (int j = 0; j < T; ++j) {
-        const int ks = j % AT_KS, sb = j % AT_SS;
-        mbar_wait(&k_full[ks], (j / AT_KS) & 1);
-        tc_fence_after();
-        const uint32_t k_base = smem_u32(smem + OFF_K + ks * TILE_BYTES);
-#pragma unroll
-        for (int k = 0; k < AT_D / 16; ++k)
-          umma_bf16(TM_S + sb * AT_BN, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s,
-                    k != 0 ? 1u : 0u);
-        umma_commit(&s_full[sb]);
-        umma_commit(&k_empty[ks]);
-        if (j >= 2) issue_pv(j - 2);
+        mbar_wait(&v_empty[vs], vph);
+        mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+        tma_load_4d(smem + OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
+        if (++vs == AT_VS) { vs = 0; vph ^= 1; }
       }
-      if (T >= 2) issue_pv(T - 2);
-      issue_pv(T - 1);
+    }
+  } else {
+    static_assert(AT_KS == 3 && AT_VS == 3 && AT_SS == 3, "the issue loops are unrolled by the common ring depth");
+    if (elect_one()) {
+      constexpr uint64_t DESC_HI = (uint64_t)((1024u >> 4) | (1u << 14) | (2u << 29)) << 32;   // SBO, version, SW128
+      const uint32_t dlo = ((smem_u32(smem) >> 4) & 0x3FFFu) | (1u << 16);  // + (byte offset >> 4): no carry, smem < 256 KiB
+      auto desc_at = [&](uint32_t lo, uint32_t byte_off) -> uint64_t { return DESC_HI | (uint64_t)(lo + (byte_off >> 4)); };
+      if (warp == 1) {
+        // ===================== MMA issuer: scores =====================
+        constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+        mbar_wait(q_full, 0);
+        int j = 0;
+        for (uint32_t r = 0; j < T; ++r) {
+          const uint32_t par = r & 1;
+#pragma unroll
+          for (int st = 0; st < 3; ++st) {
+            if (j < T) {
+              uint32_t lo = dlo;
+              asm volatile("" : "+r"(lo));                   // per tile: keeps ptxas from hoisting (and spilling) 24 descriptors
+              mbar_wait(&k_full[st], par);
+              if (r >= 1) mbar_wait(&s_empty[st], par ^ 1);   // P V of tile j - 3 has read P out of this stage
+              tc_fence_after();
+#pragma unroll
+              for (int k = 0; k < AT_D / 16; ++k)
+                umma_bf16(TM_S + st * AT_BN, desc_at(lo, OFF_Q + k * 32), desc_at(lo, OFF_K + st * TILE_BYTES + k * 32), idesc_s,
+                          k != 0 ? 1u : 0u);
+              umma_commit(&s_full[st]);
+              umma_commit(&k_empty[st]);
+              ++j;
+            }
+          }
+        }
+      } else {
+        // ===================== MMA issuer: P V =====================
+        // A = P from TMEM (bf16 pairs over the first 64 columns of the tile's S stage; 16 keys = 8 columns), B = V
+        // MN-major.  O[i & 1] accumulates over all of a group's tiles; the softmax rescales it in place when its row
+        // max moves.
+        constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+        int i = 0;
+        for (uint32_t r = 0; i < T; ++r) {
+          const uint32_t par = r & 1;
+#pragma unroll
+          for (int st = 0; st < 3; ++st) {
+            if (i < T) {
+              const uint32_t ob = i & 1;
+              uint32_t lo = dlo;
+              asm volatile("" : "+r"(lo));
+              mbar_wait(&v_full[st], par);
+              mbar_wait(&p_full[st], par);
+              tc_fence_after();
+#pragma unroll
+              for (int kk = 0; kk < AT_BN / 16; ++kk) {
+                umma_bf16_ts(TM_O + ob * AT_D, TM_S + st * AT_BN + kk * 8, desc_at(lo, OFF_V + st * TILE_BYTES + kk * 16 * 128),
+                             idesc_o, (i >= 2 || kk != 0) ? 1u : 0u);
+              }
+              umma_commit(&o_full[ob]);
+              umma_commit(&v_empty[st]);
+              umma_commit(&s_empty[st]);
+              ++i;
+            }
+          }
+        }
+      }
     }
   }
   } else {
@@ -296,8 +390,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           const int i = ch * 8 + h * 2;
           float x0, x1;
           ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
-          const float p0 = ex2_approx(x0);
-          const float p1 = ex2_approx(x1);
+          float p0, p1;
+          ex2_pair(i >> 1, p0, p1, x0, x1);
           fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
           pk[i >> 1] = pack_bf16x2(p0, p1);
         }
@@ -417,7 +511,8 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
   uint64_t* p_full = s_full + AT_SS;       // AT_SS
   uint64_t* o_full = p_full + AT_SS;       // 2
   uint64_t* o_empty = o_full + 2;          // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
+  uint64_t* s_empty = o_empty + 2;         // AT_SS: P V of the stage has completed, the next score MMA may overwrite it
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + AT_SS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int T = (p.Nk + AT_BN - 1) / AT_BN;
@@ -436,6 +531,7 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     for (int i = 0; i < AT_VS; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int i = 0; i < AT_SS; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); }
     for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
+    for (int i = 0; i < AT_SS; ++i) mbar_init(&s_empty[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -451,10 +547,15 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
 
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    // The single-thread roles below sit on the kernel's critical path (the trace in profiles/ shows the tensor pipe
+    // idle whenever the issuing thread is between two MMA batches), so each keeps running ring positions and phase
+    // bits instead of dividing the flat tile count, and builds an operand descriptor by one add onto a precomputed
+    // word.  (Running the loops warp-converged with lane 0 issuing was tried: the compiler then wraps every
+    // tcgen05.mma in an elect / broadcast loop, which is slower than this.)
     if (warp == 0) {
       if (elect_one()) {
-        // ===================== TMA producer: runs ahead across work items =====================
-        uint32_t jj = 0;                                    // running key-tile count
+        // ===================== TMA producer for Q and K: runs ahead across work items =====================
+        uint32_t ks = 0, kph = 1;                           // ring position, parity to wait for on k_empty
         for (int wi = 0; wi < n_items; ++wi) {
           const int w = w_first + wi * pp.w_stride;
           const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
@@ -462,63 +563,108 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
           mbar_wait(&q_empty[qs], ((wi >> 1) & 1) ^ 1);
           mbar_arrive_expect_tx(&q_full[qs], TILE_BYTES);
           tma_load_4d(smem + ATP_OFF_Q + qs * TILE_BYTES, &tmQ, &q_full[qs], 0, head, qt * AT_BM, b);
-          for (int j = 0; j < T; ++j, ++jj) {
-            const int ks = jj % AT_KS, vs = jj % AT_VS;
-            mbar_wait(&k_empty[ks], ((jj / AT_KS) & 1) ^ 1);
+          for (int j = 0; j < T; ++j) {
+            mbar_wait(&k_empty[ks], kph);
             mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
             tma_load_4d(smem + ATP_OFF_K + ks * TILE_BYTES, &tmK, &k_full[ks], 0, head, j * AT_BN, b);
-            mbar_wait(&v_empty[vs], ((jj / AT_VS) & 1) ^ 1);
-            mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
-            tma_load_4d(smem + ATP_OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
+            if (++ks == AT_KS) { ks = 0; kph ^= 1; }
           }
         }
       }
-    } else if (warp == 1) {
+    } else if (warp == 3) {
       if (elect_one()) {
-        // ===================== MMA issuer: one flat sequence of key tiles over all items =====================
-        constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
-        constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
-        const uint32_t total_tiles = (uint32_t)n_items * (uint32_t)T;
-        // P V of running tile i (item i / T, tile i % T of it; group = that tile's parity inside the item)
-        auto issue_pv = [&](uint32_t i) {
-          const uint32_t wi = i / (uint32_t)T, wj = i - wi * (uint32_t)T;
-          const int pb = i % AT_SS, vs = i % AT_VS, ob = wj & 1;
-          if (wj < 2 && wi >= 1) {            // first P V of this group in a new item overwrites O[ob]:
-            mbar_wait(&o_empty[ob], (wi - 1) & 1);   // the group has read the previous item's result out of it
+        // ===================== TMA producer for V: its own thread, so a full V ring never holds back a K load ========
+        uint32_t vs = 0, vph = 1;
+        for (int wi = 0; wi < n_items; ++wi) {
+          const int w = w_first + wi * pp.w_stride;
+          const int head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
+          for (int j = 0; j < T; ++j) {
+            mbar_wait(&v_empty[vs], vph);
+            mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+            tma_load_4d(smem + ATP_OFF_V + vs * TILE_BYTES, &tmV, &v_full[vs], 0, head, j * AT_BN, b);
+            if (++vs == AT_VS) { vs = 0; vph ^= 1; }
           }
-          mbar_wait(&p_full[pb], (i / AT_SS) & 1);
-          mbar_wait(&v_full[vs], (i / AT_VS) & 1);
-          tc_fence_after();
-          const uint32_t p_tmem = TM_S + pb * AT_BN;
-          const uint32_t v_base = smem_u32(smem + ATP_OFF_V + vs * TILE_BYTES);
-#pragma unroll
-          for (int kk = 0; kk < AT_BN / 16; ++kk) {
-            umma_bf16_ts(TM_O + ob * AT_D, p_tmem + kk * 8, umma_desc_sw128_mn(v_base + kk * 16 * 128), idesc_o,
-                         (wj >= 2 || kk != 0) ? 1u : 0u);
-          }
-          umma_commit(&o_full[ob]);
-          umma_commit(&v_empty[vs]);
-        };
-        uint32_t wi = 0, j = 0;
-        for (uint32_t jj = 0; jj < total_tiles; ++jj) {
-          const int ks = jj % AT_KS, sb = jj % AT_SS, qs = wi & 1;
-          if (j == 0) mbar_wait(&q_full[qs], (wi >> 1) & 1);
-          mbar_wait(&k_full[ks], (jj / AT_KS) & 1);
-          tc_fence_after();
-          const uint32_t q_base = smem_u32(smem + ATP_OFF_Q + qs * TILE_BYTES);
-          const uint32_t k_base = smem_u32(smem + ATP_OFF_K + ks * TILE_BYTES);
-#pragma unroll
-          for (int k = 0; k < AT_D / 16; ++k)
-            umma_bf16(TM_S + sb * AT_BN, umma_desc_sw128(q_base + k * 32), umma_desc_sw128(k_base + k * 32), idesc_s,
-                      k != 0 ? 1u : 0u);
-          umma_commit(&s_full[sb]);
-          umma_commit(&k_empty[ks]);
-          if (j == (uint32_t)T - 1) umma_commit(&q_empty[qs]);   // the item's score MMAs are all issued
-          if (jj >= 2) issue_pv(jj - 2);
-          if (++j == (uint32_t)T) { j = 0; ++wi; }
         }
-        if (total_tiles >= 2) issue_pv(total_tiles - 2);
-        issue_pv(total_tiles - 1);
+      }
+    } else {
+      // ===================== MMA issuers: warp 1 the score products, warp 2 the P V products =====================
+      // Two threads, because one thread's address and barrier arithmetic between two batches is what the tensor pipe
+      // waited on; tcgen05 operations of different threads are not ordered, so the one hazard the single issuer
+      // resolved by program order — the score MMA of tile j + 3 overwriting the S / P stage P V of tile j reads — is
+      // carried by s_empty.  Both loops are unrolled by the ring depth: tile 3r + st sits in stage st of every ring
+      // with parity r & 1, so barrier addresses and descriptors are immediates on one base.
+      static_assert(AT_KS == 3 && AT_VS == 3 && AT_SS == 3, "the issue loops are unrolled by the common ring depth");
+      if (elect_one()) {
+#ifdef MDX_ATTN_TRACE
+        int tr_n = 0;
+#endif
+        constexpr uint64_t DESC_HI = (uint64_t)((1024u >> 4) | (1u << 14) | (2u << 29)) << 32;   // SBO, version, SW128
+        const uint32_t dlo = ((smem_u32(smem) >> 4) & 0x3FFFu) | (1u << 16);  // + (byte offset >> 4): no carry, smem < 256 KiB
+        auto desc_at = [&](uint32_t lo, uint32_t byte_off) -> uint64_t { return DESC_HI | (uint64_t)(lo + (byte_off >> 4)); };
+        const uint32_t total_tiles = (uint32_t)n_items * (uint32_t)T;
+        if (warp == 1) {
+          constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN);
+          uint32_t wi = 0, j = 0, jj = 0;                    // (item, tile inside it), flat tile count
+          for (uint32_t r = 0; jj < total_tiles; ++r) {
+            const uint32_t par = r & 1;
+#pragma unroll
+            for (int st = 0; st < 3; ++st) {
+              if (jj < total_tiles) {
+                const uint32_t qs = wi & 1;
+                uint32_t lo = dlo;
+                asm volatile("" : "+r"(lo));                 // per tile: keeps ptxas from hoisting (and spilling) 24 descriptors
+                if (j == 0) mbar_wait(&q_full[qs], (wi >> 1) & 1);
+                mbar_wait(&k_full[st], par);
+                if (r >= 1) mbar_wait(&s_empty[st], par ^ 1);
+                AT_TR(0, 1, jj);
+                tc_fence_after();
+                const uint32_t q_off = ATP_OFF_Q + qs * TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < AT_D / 16; ++k)
+                  umma_bf16(TM_S + st * AT_BN, desc_at(lo, q_off + k * 32), desc_at(lo, ATP_OFF_K + st * TILE_BYTES + k * 32),
+                            idesc_s, k != 0 ? 1u : 0u);
+                umma_commit(&s_full[st]);
+                umma_commit(&k_empty[st]);
+                if (j == (uint32_t)T - 1) umma_commit(&q_empty[qs]);   // the item's score MMAs are all issued
+                AT_TR(0, 2, jj);
+                if (++j == (uint32_t)T) { j = 0; ++wi; }
+                ++jj;
+              }
+            }
+          }
+        } else {
+          constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(AT_BM, AT_D);
+          uint32_t pwi = 0, pj = 0, i = 0;
+          for (uint32_t r = 0; i < total_tiles; ++r) {
+            const uint32_t par = r & 1;
+#pragma unroll
+            for (int st = 0; st < 3; ++st) {
+              if (i < total_tiles) {
+                const uint32_t ob = pj & 1;
+                uint32_t lo = dlo;
+                asm volatile("" : "+r"(lo));
+                if (pj < 2 && pwi >= 1) {       // first P V of this group in a new item overwrites O[ob]:
+                  mbar_wait(&o_empty[ob], (pwi - 1) & 1);    // the group has read the previous item's result out of it
+                }
+                mbar_wait(&v_full[st], par);
+                mbar_wait(&p_full[st], par);
+                AT_TR(3, 3, i);
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < AT_BN / 16; ++kk) {
+                  umma_bf16_ts(TM_O + ob * AT_D, TM_S + st * AT_BN + kk * 8,
+                               desc_at(lo, ATP_OFF_V + st * TILE_BYTES + kk * 16 * 128), idesc_o, (pj >= 2 || kk != 0) ? 1u : 0u);
+                }
+                umma_commit(&o_full[ob]);
+                umma_commit(&v_empty[st]);
+                umma_commit(&s_empty[st]);
+                AT_TR(3, 5, i);
+                if (++pj == (uint32_t)T) { pj = 0; ++pwi; }
+                ++i;
+              }
+            }
+          }
+        }
       }
     }
   } else {
@@ -533,6 +679,9 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     float* xch = reinterpret_cast<float*>(smem + ATP_OFF_XCH);
     float* xml = reinterpret_cast<float*>(smem + ATP_OFF_XML);
     uint32_t pvc = 0;                                        // P V completions of this group waited for so far
+#ifdef MDX_ATTN_TRACE
+    int tr_n = (qw == 0 && lane == 0) ? 0 : AT_TR_N;
+#endif
     for (int wi = 0; wi < n_items; ++wi) {
       const int w = w_first + wi * pp.w_stride;
       const int qt = w % pp.nqt, head = (w / pp.nqt) % pp.heads, b = w / (pp.nqt * pp.heads);
@@ -542,7 +691,9 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
       for (int j = g; j < T; j += 2, ++it) {
         const uint32_t jj = (uint32_t)wi * (uint32_t)T + (uint32_t)j;
         const int sb = jj % AT_SS;
+        AT_TR(1 + g, 0, jj);
         mbar_wait(&s_full[sb], (jj / AT_SS) & 1);
+        AT_TR(1 + g, 1, jj);
         tc_fence_after();
         const uint32_t ts = TM_S + lane_off + sb * AT_BN;
         const int key0 = j * AT_BN;
@@ -550,6 +701,7 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
 #pragma unroll
         for (int cc = 0; cc < AT_BN / 32; ++cc) tmem_ld32(ts + cc * 32, *reinterpret_cast<uint32_t(*)[32]>(&sr[cc * 32]));
         tmem_ld_wait();
+        AT_TR(1 + g, 2, jj);
         if (key0 + AT_BN > p.Nk) {
 #pragma unroll
           for (int i = 0; i < AT_BN; ++i)
@@ -571,10 +723,12 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
           l_run *= alpha;
           m_run = mx;
         }
+        AT_TR(1 + g, 3, jj);
         if (it >= 1) {
           mbar_wait(&o_full[g], pvc & 1);
           ++pvc;
           if (__any_sync(0xffffffffu, moved)) {
+            AT_TR(1 + g, 7, jj);
             tc_fence_after();
 #pragma unroll
             for (int cc = 0; cc < AT_D / 32; ++cc) {
@@ -593,6 +747,7 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
             tmem_st_wait();
           }
         }
+        AT_TR(1 + g, 4, jj);
         float rs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float nmsc = -m_run * c;
         uint32_t pk[AT_BN / 2];
@@ -603,18 +758,20 @@ attn_tc_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
             const int i = ch * 8 + h * 2;
             float x0, x1;
             ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
-            const float p0 = ex2_approx(x0);
-            const float p1 = ex2_approx(x1);
+            float p0, p1;
+            ex2_pair(i >> 1, p0, p1, x0, x1);
             fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
             pk[i >> 1] = pack_bf16x2(p0, p1);
           }
         }
+        AT_TR(1 + g, 5, jj);
         tmem_st32(ts, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
         tmem_st32(ts + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
         tmem_st_wait();
         l_run += ((rs8[0] + rs8[1]) + (rs8[2] + rs8[3])) + ((rs8[4] + rs8[5]) + (rs8[6] + rs8[7]));
         tc_fence_before();
         mbar_arrive(&p_full[sb]);
+        AT_TR(1 + g, 6, jj);
       }
       // ---- this group's output row of the item, then hand O[g] back to the MMA thread ----
       float o_acc[AT_D];
@@ -789,7 +946,8 @@ attn_tc_single_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     for (int i = 0; i < AT_BN; i += 2) {
       float x0, x1;
       ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
-      const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+      float p0, p1;
+      ex2_pair(i >> 1, p0, p1, x0, x1);
       fadd2(rs8[i & 6], rs8[(i & 6) + 1], p0, p1);
       pk[i >> 1] = pack_bf16x2(p0, p1);
     }
@@ -986,7 +1144,8 @@ attn_tc_single_persistent_kernel(const __grid_constant__ CUtensorMap tmQ, const 
             const int i = ch * 8 + h * 2;
             float x0, x1;
             ffma2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, nmsc);
-            const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+            float p0, p1;
+            ex2_pair(i >> 1, p0, p1, x0, x1);
             fadd2(rs8[2 * h], rs8[2 * h + 1], p0, p1);
             pk[i >> 1] = pack_bf16x2(p0, p1);
           }
@@ -1078,6 +1237,11 @@ int make_map_qkv(CUtensorMap* m, const void* ptr, long long ld, int d, int heads
 }  // namespace
 
 // Internal entry (called by mdx_attention for bf16, d <= 64, d % 8 == 0, not causal).
+#ifdef MDX_ATTN_TRACE
+extern "C" int mdx_attn_trace_dump(uint32_t* host, int n_words) {
+  return (int)cudaMemcpyFromSymbol(host, at_trace, sizeof(uint32_t) * n_words);
+}
+#endif
 int mdx_attention_tc_d64(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                          void* o, long long ldo, int batch, int heads, int Nq, int Nk, int d, float scale,
                          cudaStream_t st) {

@@ -354,14 +354,16 @@ int launch_gn(GnP p, cudaStream_t st) {
   const int C = p.C1 + p.C2;
   p.CV = C / 8;
   MDX_CHECK_ARG(p.CV <= 512, "mdx_groupnorm: too many channels (%d)", C);
-  p.RP = 512 / p.CV;
+  static const int blk = getenv("MDX_GN_BLOCK") ? atoi(getenv("MDX_GN_BLOCK")) : 256;   // threads per block: four small blocks per SM hide each other's prologue better than two of 512 (profiles/r02_gn_apply_ab_block.txt)
+  p.RP = (p.CV <= blk ? blk : 512) / p.CV;
+  if (p.RP < 1) p.RP = 1;
   if (p.RP > 16) p.RP = 16;
   // a few waves of blocks (MDX_GN_APPLY_BLOCKS resident per SM): enough that the last, partly filled wave is cheap,
   // few enough that a block's prologue (statistics -> per-channel scale / shift) is amortised over many rows; each
   // block walks at least 8*RP rows (4-deep unrolled loads twice)
   int chunks = (p.HW + 8 * p.RP - 1) / (8 * p.RP);
   static const int waves = getenv("MDX_GN_WAVES") ? atoi(getenv("MDX_GN_WAVES")) : 4;   // A/B switch
-  int want = (MDX_GN_APPLY_BLOCKS * waves * mdx_num_sms() + p.n - 1) / p.n;
+  int want = (MDX_GN_APPLY_BLOCKS * (512 / (p.CV * p.RP) > 1 ? 512 / (p.CV * p.RP) : 1) * waves * mdx_num_sms() + p.n - 1) / p.n;
   if (chunks > want) chunks = want;
   if (chunks < 1) chunks = 1;
   p.rows_per_block = (p.HW + chunks - 1) / chunks;
