@@ -146,7 +146,7 @@ __device__ uint32_t at_trace[4 * AT_TR_N * 2];
 #endif
 // exp2 of the pair with index k of a score row: the MUFU for most pairs, the FMA-pipe form for the chosen share
 __device__ __forceinline__ void ex2_pair(int k, float& p0, float& p1, float x0, float x1) {
-  if ((k % MDX_ATTN_POLY_DEN) < MDX_ATTN_POLY_NUM) {
+  if ((k % MDX_ATTN_POLY_DEN) < MDX_ATTN_POLY_NUM) {         // neighbouring pairs: spreading them evenly measured 1.5 % slower
     ex2_poly2(p0, p1, x0, x1);
   } else {
     p0 = ex2_approx(x0);

@@ -60,6 +60,14 @@ struct TcParams {
   int stat_slots;      // slots per image
   int debug;        // MDX_GEMM_DEBUG bit mask (profiling only): 1 = no global stores, 2 = epilogue does nothing
   int b_resident;   // K fits the B ring: each CTA keeps ONE n-tile's weight slice in smem and streams only A tiles
+  // Cluster launch (0 = none, else the cluster size 2 or 4).  The persistent schedule gives consecutive blocks
+  // consecutive tiles, n fastest, so the CTAs of a cluster hold mc_gn neighbouring n-tiles of mc / mc_gn m-tiles at the
+  // same time.  CTAs on the same m-tile each fetch 1 / mc_gn of every A block and multicast it to that group; CTAs on the
+  // same n-tile (2 x 2 clusters) do the same with the B block.  The tensor maps then hold the sub-boxes.
+  int mc, mc_gn;
+  int mc_cy, mc_cx;             // the A tile is cut into (tn / mc_sn) x mc_cy x mc_cx sub-boxes of mc_sn x mc_sy x mc_sx
+  int mc_sn, mc_sy, mc_sx;      // images x rows x pixels, numbered in row order of the tile
+  int mc_grid_cap;  // host only: CTAs the device keeps resident in clusters of this size (the schedule is persistent)
   void* out;
   long long ldc;
   int out_f32;
@@ -504,7 +512,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+      // multicast: a stage is rewritten by every CTA this one shares A or B with, so all of them must have drained it
+      mbar_init(&empty[i], p.mc ? p.mc_gn + ((p.mc / p.mc_gn == 2 && !p.b_resident) ? 1 : 0) : 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
@@ -519,6 +528,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  if (p.mc) cluster_sync_all();             // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -550,17 +560,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       int stage = 0;
       uint32_t phase = 0;
       int m_tile, n_tile;
+      // cluster rank -> (rn, rm): which n-tile / m-tile of the cluster; rn is also which slice of A this CTA fetches,
+      // rm which slice of B
+      const int rank = p.mc ? (int)cluster_ctarank() : 0;
+      const int gn = p.mc ? p.mc_gn : 1;
+      const int rn = rank % gn, rm = rank / gn;
+      const int gm = (p.mc && p.mc / p.mc_gn == 2) ? 2 : 1;     // B pieces per block (resident slices are loaded whole, unshared)
+      const uint16_t a_mask = (uint16_t)(((1u << gn) - 1u) << (rm * gn));                  // same m-tile
+      const uint16_t b_mask = (uint16_t)((gm == 2 ? (1u | (1u << gn)) : 1u) << rn);          // same n-tile
+      const int a_slice = rn * (A_STAGE_BYTES / gn);
+      const int b_rows = BN / gm, b_slice = rm * (Cfg::B_STAGE_BYTES / gm);
+      int a_dn = 0, a_dy = 0, a_dx = 0;
+      if (p.mc) {
+        a_dn = (rn / (p.mc_cy * p.mc_cx)) * p.mc_sn;
+        a_dy = ((rn / p.mc_cx) % p.mc_cy) * p.mc_sy;
+        a_dx = (rn % p.mc_cx) * p.mc_sx;
+      }
       if (p.b_resident && tile_at(0, m_tile, n_tile)) {
         mbar_arrive_expect_tx(bfull, p.total_kb * Cfg::B_STAGE_BYTES);
         for (int kb = 0; kb < p.total_kb; ++kb)
-          tma_load_2d(sB + kb * Cfg::B_STAGE_BYTES, &tmB, bfull, kb * BK, n_tile * BN);
+          for (int h = 0; h < gm; ++h)        // (the B map holds a 1 / gm box; the resident slice is not shared)
+            tma_load_2d(sB + kb * Cfg::B_STAGE_BYTES + h * (Cfg::B_STAGE_BYTES / gm), &tmB, bfull, kb * BK, n_tile * BN + h * b_rows);
       }
       const uint32_t stage_tx = p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + Cfg::B_STAGE_BYTES;
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
         const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);
-        const int x0 = (m_tile - m_row * p.tiles_x) * p.tw;
-        const int y0 = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th;
-        const int n0 = (int)fdiv((uint32_t)m_tile, p.fd_tpi) * p.tn;
+        const int x0 = (m_tile - m_row * p.tiles_x) * p.tw + a_dx;
+        const int y0 = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th + a_dy;
+        const int n0 = (int)fdiv((uint32_t)m_tile, p.fd_tpi) * p.tn + a_dn;
         int kcoord = 0;
         for (int seg = 0; seg < p.nseg; ++seg) {
           const CUtensorMap* tm = seg == 0 ? &tmA0 : (seg == 1 ? &tmA1 : &tmA2);
@@ -572,8 +599,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             for (int cb = 0; cb < nkb; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
               mbar_arrive_expect_tx(&full[stage], stage_tx);
-              tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 * p.stride + dx, y0 * p.stride + dy, n0);
-              if (!p.b_resident) tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
+              if (p.mc)
+                tma_load_4d_mc(sA + stage * A_STAGE_BYTES + a_slice, tm, &full[stage], cb * BK, x0 * p.stride + dx,
+                               y0 * p.stride + dy, n0, a_mask);
+              else
+                tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 * p.stride + dx, y0 * p.stride + dy, n0);
+              if (!p.b_resident) {
+                if (gm == 2)                                   // (streaming only: shared with the CTA on the same n-tile)
+                  tma_load_2d_mc(sB + stage * Cfg::B_STAGE_BYTES + b_slice, &tmB, &full[stage], kcoord, n_tile * BN + rm * b_rows, b_mask);
+                else
+                  tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
+              }
               kcoord += BK;
               if (++stage == STAGES) {
                 stage = 0;
@@ -592,6 +628,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       uint32_t phase = 0;
       uint32_t iter = 0;
       int m_tile, n_tile;
+      uint16_t mc_mask = 1;
+      if (p.mc) {
+        const int rank = (int)cluster_ctarank(), gn = p.mc_gn, gm = p.mc / p.mc_gn;
+        const int rn = rank % gn, rm = rank / gn;
+        mc_mask = (uint16_t)((((1u << gn) - 1u) << (rm * gn)) | (((gm == 2 && !p.b_resident) ? (1u | (1u << gn)) : 1u) << rn));
+      }
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
         const uint32_t as = iter & 1;
         const uint32_t aph = (iter >> 1) & 1;
@@ -609,7 +651,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             umma_bf16(d_tmem, umma_desc_sw128(a_base + k * 32), umma_desc_sw128(b_base + k * 32), idesc,
                       (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty[stage]);  // smem slot reusable once these MMAs retire
+          if (p.mc) umma_commit_mc(&empty[stage], mc_mask);   // ... in this CTA and in every CTA that also writes it
+          else umma_commit(&empty[stage]);  // smem slot reusable once these MMAs retire
           if (kb == p.total_kb - 1) umma_commit(&tfull[as]);
           if (++stage == STAGES) {
             stage = 0;
@@ -778,6 +821,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 
   tc_fence_before();
   __syncthreads();
+  if (p.mc) cluster_sync_all();             // no CTA leaves while its peer may still signal or write into it
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -876,23 +920,84 @@ int launch_tc_epi(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams
                                         TcCfg<BN>::SMEM_BYTES));
     attr.mark();
   }
-  gemm_tc_kernel<BN, EPI><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
+  if (q.mc) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(TcCfg<BN>::THREADS);
+    cfg.dynamicSmemBytes = TcCfg<BN>::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)q.mc; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    MDX_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, EPI>, maps[0], maps[1], maps[2], mb, q));
+  } else {
+    gemm_tc_kernel<BN, EPI><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
+  }
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;
 }
 
+// How many CTAs of this block shape the device keeps resident when they are launched as clusters of `cs` (a GPC whose
+// free SMs are not a multiple of the cluster size leaves some without partners); 0 = cluster launch not possible.
+// Cached per device and size.
+template <int BN>
+int max_clustered_ctas(int cs) {
+  static int cached[64][2];
+  static MdxPerDeviceOnce once;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || (cs != 2 && cs != 4)) return 0;
+  if (once.need()) {
+    for (int i = 0; i < 2; ++i) {
+      const int c = i == 0 ? 2 : 4;
+      int n = 0;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)(c * num_sms()));
+      cfg.blockDim = dim3(TcCfg<BN>::THREADS);
+      cfg.dynamicSmemBytes = TcCfg<BN>::SMEM_BYTES;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = (unsigned)c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      if (cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI_GENERIC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               TcCfg<BN>::SMEM_BYTES) != cudaSuccess ||
+          cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, EPI_GENERIC>, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+      }
+      cached[dev][i] = c * n;
+      if (getenv("MDX_GEMM_MC_VERBOSE"))
+        fprintf(stderr, "mdx_gemm_tc: BN=%d: %d CTAs resident in clusters of %d (%d SMs)\n", BN, c * n, c, num_sms());
+    }
+    once.mark();
+  }
+  return cached[dev][cs == 2 ? 0 : 1];
+}
+
 template <int BN>
 int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p, cudaStream_t st) {
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  if (p.mc && grid > p.mc_grid_cap) grid = p.mc_grid_cap;
+  if (p.mc) grid -= grid % p.mc;            // (num_tiles is a multiple of the cluster size, see mdx_gemm_tc)
   TcParams q = p;
   if (const char* dbg = getenv("MDX_GEMM_DEBUG")) q.debug = atoi(dbg);
   const bool no_resident = getenv("MDX_GEMM_NO_RESIDENT") != nullptr;  // A/B switch for tests and profiling
   // weights stay in smem when the whole K fits the B ring and every CTA would otherwise re-fetch them >= 3 times
   if (!no_resident && p.nseg == 1 && p.seg_taps[0] == 1 && p.total_kb <= TcCfg<BN>::STAGES &&
-      p.n_tiles_n <= num_sms() && (long long)p.m_tiles * p.n_tiles_n >= 3ll * num_sms()) {
+      p.n_tiles_n <= (p.mc ? p.mc_grid_cap : num_sms()) && (long long)p.m_tiles * p.n_tiles_n >= 3ll * num_sms()) {
     q.b_resident = 1;
-    grid = (num_sms() / p.n_tiles_n) * p.n_tiles_n;
+    const int avail = p.mc && p.mc_grid_cap < num_sms() ? p.mc_grid_cap : num_sms();
+    int unit = p.n_tiles_n;                  // whole rows of n-tiles, and whole clusters
+    while (p.mc && unit % p.mc) unit += p.n_tiles_n;
+    grid = (avail / unit) * unit;
+    if (grid == 0) { q.b_resident = 0; grid = p.num_tiles < avail ? p.num_tiles : avail; grid -= p.mc ? grid % p.mc : 0; }
+  }
+  if (q.mc && (grid <= 0 || grid % q.mc)) {
+    mdx_set_error("mdx_gemm_tc: internal: grid %d does not divide into clusters of %d", grid, q.mc);
+    return MDX_ERR_INVALID;
   }
   if (q.geglu) return launch_tc_epi<BN, EPI_GEGLU>(maps, mb, q, grid, st);
   // epi_fast: no activation, no profiling switch, a per-image bias only when a tile never straddles two images, row
@@ -1043,14 +1148,72 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     p.hw_out *= 4;
   }
 
+  // Cluster launch: the persistent schedule puts consecutive blocks on consecutive tiles, n fastest, so the CTAs of a
+  // cluster of 2 or 4 work on neighbouring n-tiles of the same m-tile (and, when there are only two n-tiles, on two
+  // m-tiles) at the same time.  Each A block is then fetched once per m-tile and each B block once per n-tile of the
+  // cluster — every CTA loads its share of the box and multicasts it — which takes 22 % (pairs) to 50 % (2 x 2) off
+  // the L2 -> SM traffic the large convolutions are bound by (ncu: L2 76 % busy next to a tensor pipe 83 % busy).
+  // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
+  // hung the GPU: every operand must be an ordinary allocation of the current device, anything else takes the
+  // plain launch.
+  int btw = p.tw, bth = p.th, btn = p.tn, b_box = bn;
+  {
+    // Default: convolutions only (any segment with taps) — alternating in-process A/B in the power-capped steady state
+    // (tools/gemm_mc_ab.py, profiles/r02_gemm_cluster_ab.txt): 3x3 convs -3 .. -9 %, 1x1 / dense layers 0 .. +2.5 %.
+    // MDX_GEMM_MC = 0 / 2 / 4 forces the largest cluster tried for every eligible launch (tests and A/B runs).
+    const char* mc_env = getenv("MDX_GEMM_MC");
+    bool has_taps = false;
+    for (int s = 0; s < a->nseg; ++s) has_taps = has_taps || a->seg_taps[s] > 1;
+    const int mc_max = mc_env ? atoi(mc_env) : (has_taps ? 4 : 0);
+    int cs = 0, gn = 1;
+    if (mc_max >= 4 && p.n_tiles_n % 4 == 0 && p.num_tiles % 4 == 0) { cs = 4; gn = 4; }
+    else if (mc_max >= 4 && p.n_tiles_n == 2 && p.num_tiles % 4 == 0) { cs = 4; gn = 2; }
+    else if (mc_max >= 2 && p.n_tiles_n % 2 == 0) { cs = 2; gn = 2; }
+    int cur = -1;
+    bool ok = cs != 0 && cudaGetDevice(&cur) == cudaSuccess;
+    auto local = [&](const void* ptr) {
+      cudaPointerAttributes pa;
+      if (cudaPointerGetAttributes(&pa, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+      return pa.type == cudaMemoryTypeDevice && pa.device == cur;
+    };
+    for (int s = 0; ok && s < a->nseg; ++s) ok = local(a->a[s]);
+    if (ok) ok = local(a->b);
+    int cap = 0;
+    for (; ok && cs >= 2; cs >>= 1) {         // a few SMs without partners are a fair price; far fewer is not
+      switch (bn) {
+        case 64: cap = max_clustered_ctas<64>(cs); break;
+        case 128: cap = max_clustered_ctas<128>(cs); break;
+        case 160: cap = max_clustered_ctas<160>(cs); break;
+        case 192: cap = max_clustered_ctas<192>(cs); break;
+        default: cap = max_clustered_ctas<256>(cs); break;
+      }
+      if (cap >= cs && cap * 16 >= num_sms() * 15) break;
+      gn = 2;                                 // fall back from 4 to pairs along n
+    }
+    if (ok && cs >= 2) {
+      p.mc = cs;
+      p.mc_gn = gn;
+      p.mc_grid_cap = cap;
+      // A sub-box: halve the outermost dimension the tile spans until 1 / gn is left — its pieces are then consecutive
+      // row ranges of the tile, numbered in row order
+      for (int g = gn; g > 1; g >>= 1) {
+        if (btn > 1) btn >>= 1;
+        else if (bth > 1) bth >>= 1;
+        else btw >>= 1;
+      }
+      p.mc_sn = btn; p.mc_sy = bth; p.mc_sx = btw;
+      p.mc_cy = p.th / bth; p.mc_cx = p.tw / btw;
+      if (cs / gn == 2) b_box = bn / 2;       // 2 x 2: the CTAs on the same n-tile fetch half of the B block each
+    }
+  }
   CUtensorMap maps[3];
   for (int s = 0; s < 3; ++s) {
     int src = s < a->nseg ? s : 0;
-    int rc = make_map_a(&maps[s], a->a[src], a->lda[src], a->seg_c[src], a->W, a->H, a->n_img, p.tw, p.th, p.tn, stride);
+    int rc = make_map_a(&maps[s], a->a[src], a->lda[src], a->seg_c[src], a->W, a->H, a->n_img, btw, bth, btn, stride);
     if (rc) return rc;
   }
   CUtensorMap mb;
-  int rc = make_map_b(&mb, a->b, ktot, a->N, bn);
+  int rc = make_map_b(&mb, a->b, ktot, a->N, b_box);
   if (rc) return rc;
 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

@@ -112,6 +112,63 @@ def test_gemm_tc_conv3x3_stride2(n, H, W, Cin, Cout):
         assert torch.allclose(sums[:, 1], (ref * ref).sum(dim=(1, 2)), rtol=1e-3, atol=1e-2)
 
 
+@pytest.mark.parametrize("case", ["conv N=320 (2x2 cluster)", "conv N=640 (4x1)", "conv N=960 (pairs)", "1x1 K=320 resident",
+                                  "1x1 N=1280 resident 4x1", "stride 2", "geglu", "small image tn=2", "odd m-tiles"])
+def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
+    """The cluster launches (MDX_GEMM_MC: clusters of 4 / 2 / none; every CTA fetches a share of the A — and in 2 x 2
+    clusters of the B — block and multicasts it) change only who loads what: the accumulation order of a tile is the
+    same, so outputs and epilogue statistics must be bit-identical across the three, and right against F.conv2d."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(len(case))
+    kw = {}
+    taps = 9
+    if case.startswith("conv N=320"):
+        n, H, W, Cin, Cout = 6, 64, 64, 64, 320
+    elif case.startswith("conv N=640"):
+        n, H, W, Cin, Cout = 5, 32, 32, 128, 640
+    elif case.startswith("conv N=960"):
+        n, H, W, Cin, Cout = 3, 16, 16, 64, 960
+    elif case == "1x1 K=320 resident":
+        n, H, W, Cin, Cout, taps = 40, 64, 64, 320, 320, 1
+    elif case == "1x1 N=1280 resident 4x1":
+        n, H, W, Cin, Cout, taps = 64, 32, 32, 256, 1280, 1
+    elif case == "stride 2":
+        n, H, W, Cin, Cout = 4, 64, 64, 64, 320
+        kw["stride"] = 2
+    elif case == "geglu":
+        n, H, W, Cin, Cout, taps = 8, 32, 32, 128, 640, 1
+    elif case == "small image tn=2":
+        n, H, W, Cin, Cout = 10, 8, 8, 64, 320
+    else:
+        n, H, W, Cin, Cout = 1, 48, 48, 64, 320          # 18 m-tiles x 2 n-tiles; with n = 1 and 24 x 24: 5 m-tiles
+        H = W = 24
+    x = bf(torch.randn(n, H, W, Cin, generator=g))
+    if taps == 9:
+        w = bf(torch.randn(Cout, Cin, 3, 3, generator=g) / (9 * Cin) ** 0.5)
+        wk = pack_k(w)
+        ref = conv_ref(x, w, None, stride=kw.get("stride", 1))
+    else:
+        w = bf(torch.randn(Cout, Cin, generator=g) / Cin ** 0.5)
+        wk = w
+        ref = x @ w.t()
+    xa = x.cuda().bfloat16()
+    if taps == 1:
+        xa = xa.view(n * H * W, Cin)
+    outs = []
+    for mc in ("4", "2", "0"):
+        monkeypatch.setenv("MDX_GEMM_MC", mc)
+        if case == "geglu":
+            from minddiffusion_b200.unet import pack_geglu
+            wg, bg, gbn = pack_geglu(w.cuda(), torch.zeros(Cout, device="cuda"))
+            outs.append(ops.gemm_tc([(xa, 1)], wg.bfloat16(), bias=bg, geglu=True, block_n=gbn))
+        else:
+            res = torch.randn(ref.numel() // Cout, Cout, generator=g).cuda() if mc == "4" else res
+            outs.append(ops.gemm_tc([(xa, taps)], wk.cuda().bfloat16(), out_dtype=torch.float32, residual=res, **kw))
+    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2])
+    if case != "geglu":
+        assert rel_err(outs[0].cpu().view(ref.shape) - res.cpu().view(ref.shape), ref) < 1e-3
+
+
 def test_gemm_tc_conv_with_fused_skip():
     """ResBlock tail: conv3x3(h) + conv1x1(concat(x1, x2)) accumulated in one TMEM tile (K-concatenation)."""
     ops = _ops()

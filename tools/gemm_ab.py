@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 # (M, N, K per tap, taps, out, residual, geglu, label)
-SHAPES = [(524288, 320, 320, 1, "f32", "f32", False, "to_out 64^2"), (131072, 640, 640, 1, "f32", "f32", False, "to_out 32^2"),
+SHAPES = [(32768, 1280, 1280, 9, "bf16", None, False, "conv3x3 16^2 C1280"), (131072, 640, 640, 9, "bf16", None, False, "conv3x3 32^2 C640"), (524288, 320, 320, 1, "f32", "f32", False, "to_out 64^2"), (131072, 640, 640, 1, "f32", "f32", False, "to_out 32^2"),
           (32768, 1280, 1280, 1, "f32", "f32", False, "to_out 16^2"), (524288, 320, 1280, 1, "bf16", "f32", False, "ff2(last) 64^2"),
           (524288, 320, 320, 1, "f32", None, False, "proj_in 64^2"), (524288, 960, 320, 1, "bf16", None, False, "qkv 64^2"),
           (524288, 2560, 320, 1, "bf16", None, True, "geglu 64^2"), (131072, 5120, 640, 1, "bf16", None, True, "geglu 32^2"),
@@ -22,7 +22,8 @@ def child():
     dt = {"f32": torch.float32, "bf16": torch.bfloat16}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     for M, N, K, taps, out_t, res_t, geglu, label in SHAPES:
-        x = (torch.randn(M // 4096, 64, 64, K, device="cuda") if taps == 9 else torch.randn(M, K, device="cuda")).bfloat16()
+        side = 16 if "16^2" in label else (32 if "32^2" in label else 64)
+        x = (torch.randn(M // side ** 2, side, side, K, device="cuda") if taps == 9 else torch.randn(M, K, device="cuda")).bfloat16()
         w = (torch.randn(N, taps * K, device="cuda") / (taps * K) ** 0.5).bfloat16()
         bias = torch.randn(N, device="cuda")
         nout = N // 2 if geglu else N
