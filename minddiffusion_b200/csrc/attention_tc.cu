@@ -3,17 +3,22 @@
 // Reference semantics: CrossAttention.construct, ldm/modules/attention.py:134-152:  softmax(q k^T * d^-1/2) v.
 //
 // One CTA = 128 queries of one (batch, head); keys/values stream through in tiles of 128.
-//   warp 0 : TMA producer   Q once, then K and V tiles (3-D boxes cut straight out of the fused [B, N, 3C] / [B, L, 2C]
-//                           projection buffers, 128-byte swizzle), two mbarrier rings
+//   warp 0 : TMA producer   Q once, then the K tiles (4-D boxes cut straight out of the fused [B, N, 3C] / [B, L, 2C]
+//                           projection buffers, 128-byte swizzle), 3-stage mbarrier ring
+//   warp 3 : TMA producer   the V tiles, its own ring — a full V ring never holds back a K load
 //   warp 1 : MMA issuer     S_j = Q K_j^T   (M128 x N128 x K64, both operands K-major)        -> TMEM S[j%3]
-//                           O_j = P_j V_j   (M128 x N64 x K128, A = P from smem, B = V MN-major) -> TMEM O[j&1]
-//   warp 2 : TMEM allocate / free (512 columns: 3 x 128 for S, 2 x 64 for O)
+//   warp 2 : MMA issuer     O_j = P_j V_j   (M128 x N64 x K128, A = P from TMEM, B = V MN-major) -> TMEM O[j&1]
+//                           (and TMEM allocate / free: 512 columns, 3 x 128 for S, 2 x 64 for O).  Two issuing threads
+//                           because one thread's scalar work between two MMA batches left the tensor pipe idle; the
+//                           ordering they lose (tcgen05 operations of different threads are unordered) is restored by
+//                           s_empty: the score MMA of tile j + 3 waits for P V of tile j to have read its stage.
 //   warps 4-11: softmax, two warpgroups ping-ponging over key tiles (group g owns tiles g, g+2, ...).  Thread =
-//                           query row (TMEM lane), so row max / row sum need no shuffles.  Two passes over S in TMEM
-//                           (max, then exp2 + sum), P written as bf16 into a 128B-swizzled smem operand.  The running
-//                           output O[g] stays in TMEM and accumulates over the group's tiles; it is rescaled in place
-//                           (tcgen05.ld / st) only when a row's max moves by more than 2^8; the two groups' (max, sum, O)
-//                           are merged at the end.
+//                           query row (TMEM lane), so row max / row sum need no shuffles.  One pass over S: the 128
+//                           scores of the row into registers, max, exp2 + sum (3 of every 16 pairs on the FMA pipe,
+//                           the rest on the MUFU), P written back as bf16 pairs over the S columns (tcgen05.st).  The
+//                           running output O[g] stays in TMEM and accumulates over the group's tiles; it is rescaled in
+//                           place (tcgen05.ld / st) only when a row's max moves by more than 2^8; the two groups'
+//                           (max, sum, O) are merged at the end.
 // Keys beyond Nk are masked to -inf (K/V rows there are zero-filled by TMA); query rows beyond Nq are not stored.
 #include "common.cuh"
 #include <atomic>
