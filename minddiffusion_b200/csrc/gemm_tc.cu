@@ -68,6 +68,9 @@ struct TcParams {
   int mc_cy, mc_cx;             // the A tile is cut into (tn / mc_sn) x mc_cy x mc_cx sub-boxes of mc_sn x mc_sy x mc_sx
   int mc_sn, mc_sy, mc_sx;      // images x rows x pixels, numbered in row order of the tile
   int mc_grid_cap;  // host only: CTAs the device keeps resident in clusters of this size (the schedule is persistent)
+  int cg2;          // 1: clusters of two as a CTA PAIR (tcgen05 cta_group::2): the pair holds two consecutive m-tiles of one
+                    // n-tile, the even CTA issues M = 256 MMAs over both SMs, each CTA loads its own A block and half of
+                    // the B block (the B map holds BLOCK_N / 2 rows).  Opt-in (MDX_GEMM_CG2=1), excludes mc.
   void* out;
   long long ldc;
   int out_f32;
@@ -84,6 +87,8 @@ struct TcParams {
 template <int BN> struct TcCfg {
   static constexpr int B_STAGE_BYTES = BN * BK * 2;
   static constexpr int STAGES = (BN >= 256) ? 3 : (BN >= 192 ? 4 : (BN >= 128 ? 5 : 7));
+  // CTA-pair form: a CTA stages only half of each B block, so the same ring space holds more stages
+  static constexpr int STAGES_CG2 = (STAGES * (A_STAGE_BYTES + B_STAGE_BYTES)) / (A_STAGE_BYTES + B_STAGE_BYTES / 2);
   static constexpr int TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
   static constexpr int EPI_WARPS = 12;                        // 4 TMEM lane quadrants x 3 column shares
   static constexpr int THREADS = 128 + 32 * EPI_WARPS;        // 512: one role warpgroup + three epilogue warpgroups
@@ -482,18 +487,21 @@ constexpr int EPI_GENERIC = 0;   // plain bf16 store, activations, profiling swi
 constexpr int EPI_GEGLU = 1;
 constexpr int EPI_FAST = 2;
 
-template <int BN, int EPI>
+// CG2: the CTA-pair form (tcgen05 cta_group::2).  A template parameter, not a runtime switch: a kernel that contains
+// cta_group::2 instructions can only be launched as a cluster ("cluster misconfiguration" otherwise).
+template <int BN, int EPI, bool CG2 = false>
 __global__ void __launch_bounds__(TcCfg<BN>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB,
                const TcParams p) {
   using Cfg = TcCfg<BN>;
-  constexpr int STAGES = Cfg::STAGES;
+  constexpr int STAGES = CG2 ? Cfg::STAGES_CG2 : Cfg::STAGES;
+  constexpr int B_BYTES = CG2 ? Cfg::B_STAGE_BYTES / 2 : Cfg::B_STAGE_BYTES;   // B bytes a CTA stages per k-block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
@@ -517,18 +525,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 32 * Cfg::EPI_WARPS);
+      mbar_init(&tempty[i], CG2 ? 2 * Cfg::EPI_WARPS : 32 * Cfg::EPI_WARPS);   // pair: one arrival per epilogue warp of both CTAs
     }
     mbar_init(bfull, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (CG2) { tmem_alloc_cg2(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish_cg2(); }
+    else { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
-  if (p.mc) cluster_sync_all();             // the peer's barriers exist before anything is multicast at them
+  if (CG2 || p.mc) cluster_sync_all();    // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -537,7 +545,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   // in L2).  Resident mode (small K): CTA b owns n-tile b % n_tiles_n for its whole life and walks m-tiles, so the
   // weight slice is fetched once per CTA instead of once per tile.
   const int cta_per_n = p.b_resident ? (int)gridDim.x / p.n_tiles_n : 1;
+  const int pair_rank = CG2 ? (int)cluster_ctarank() : 0;
   auto tile_at = [&](int it, int& m_tile, int& n_tile) -> bool {
+    if constexpr (CG2) {                     // pair c walks (two m-tiles, n-tile) items, n fastest
+      const long long item = (long long)(blockIdx.x >> 1) + (long long)it * (gridDim.x >> 1);
+      if (item >= (p.num_tiles >> 1)) return false;
+      const int pm = (int)fdiv((uint32_t)item, p.fd_ntn);
+      n_tile = (int)item - pm * p.n_tiles_n;
+      m_tile = 2 * pm + pair_rank;
+      return true;
+    }
     if (p.b_resident) {
       n_tile = (int)blockIdx.x % p.n_tiles_n;
       m_tile = (int)blockIdx.x / p.n_tiles_n + it * cta_per_n;
@@ -569,7 +586,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const uint16_t a_mask = (uint16_t)(((1u << gn) - 1u) << (rm * gn));                  // same m-tile
       const uint16_t b_mask = (uint16_t)((gm == 2 ? (1u | (1u << gn)) : 1u) << rn);          // same n-tile
       const int a_slice = rn * (A_STAGE_BYTES / gn);
-      const int b_rows = BN / gm, b_slice = rm * (Cfg::B_STAGE_BYTES / gm);
+      const int b_rows = BN / gm, b_slice = rm * (B_BYTES / gm);
       int a_dn = 0, a_dy = 0, a_dx = 0;
       if (p.mc) {
         a_dn = (rn / (p.mc_cy * p.mc_cx)) * p.mc_sn;
@@ -577,12 +594,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         a_dx = (rn % p.mc_cx) * p.mc_sx;
       }
       if (p.b_resident && tile_at(0, m_tile, n_tile)) {
-        mbar_arrive_expect_tx(bfull, p.total_kb * Cfg::B_STAGE_BYTES);
+        mbar_arrive_expect_tx(bfull, p.total_kb * B_BYTES);
         for (int kb = 0; kb < p.total_kb; ++kb)
           for (int h = 0; h < gm; ++h)        // (the B map holds a 1 / gm box; the resident slice is not shared)
-            tma_load_2d(sB + kb * Cfg::B_STAGE_BYTES + h * (Cfg::B_STAGE_BYTES / gm), &tmB, bfull, kb * BK, n_tile * BN + h * b_rows);
+            tma_load_2d(sB + kb * B_BYTES + h * (B_BYTES / gm), &tmB, bfull, kb * BK, n_tile * BN + h * b_rows);
       }
-      const uint32_t stage_tx = p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + Cfg::B_STAGE_BYTES;
+      // pair: the even CTA's barrier collects both CTAs' bytes (each loads A and half of B)
+      const uint32_t stage_tx = CG2 ? 2 * (A_STAGE_BYTES + B_BYTES)
+                                      : (p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + B_BYTES);
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
         const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);
         const int x0 = (m_tile - m_row * p.tiles_x) * p.tw + a_dx;
@@ -598,6 +617,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const int dx = taps == 9 ? tap % 3 - 1 : (taps == 4 ? p.up_px - 1 + (tap & 1) : 0);
             for (int cb = 0; cb < nkb; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
+              if constexpr (CG2) {
+                if (pair_rank == 0) mbar_arrive_expect_tx(&full[stage], stage_tx);
+                tma_load_4d_cg2(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 * p.stride + dx, y0 * p.stride + dy, n0);
+                tma_load_2d_cg2(sB + stage * B_BYTES, &tmB, &full[stage], kcoord, n_tile * BN + pair_rank * (BN / 2));
+                kcoord += BK;
+                if (++stage == STAGES) {
+                  stage = 0;
+                  phase ^= 1;
+                }
+                continue;
+              }
               mbar_arrive_expect_tx(&full[stage], stage_tx);
               if (p.mc)
                 tma_load_4d_mc(sA + stage * A_STAGE_BYTES + a_slice, tm, &full[stage], cb * BK, x0 * p.stride + dx,
@@ -606,9 +636,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 tma_load_4d(sA + stage * A_STAGE_BYTES, tm, &full[stage], cb * BK, x0 * p.stride + dx, y0 * p.stride + dy, n0);
               if (!p.b_resident) {
                 if (gm == 2)                                   // (streaming only: shared with the CTA on the same n-tile)
-                  tma_load_2d_mc(sB + stage * Cfg::B_STAGE_BYTES + b_slice, &tmB, &full[stage], kcoord, n_tile * BN + rm * b_rows, b_mask);
+                  tma_load_2d_mc(sB + stage * B_BYTES + b_slice, &tmB, &full[stage], kcoord, n_tile * BN + rm * b_rows, b_mask);
                 else
-                  tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
+                  tma_load_2d(sB + stage * B_BYTES, &tmB, &full[stage], kcoord, n_tile * BN);
               }
               kcoord += BK;
               if (++stage == STAGES) {
@@ -621,9 +651,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      // ===================== MMA issuer =====================
+    if (elect_one() && pair_rank == 0) {
+      // ===================== MMA issuer (in pair mode: the even CTA, for both SMs) =====================
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      constexpr uint32_t idesc2 = umma_idesc_bf16(2 * BM, BN);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t iter = 0;
@@ -645,15 +676,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sA + stage * A_STAGE_BYTES);
-          const uint32_t b_base = smem_u32(sB + (p.b_resident ? kb : stage) * Cfg::B_STAGE_BYTES);
+          const uint32_t b_base = smem_u32(sB + (p.b_resident ? kb : stage) * B_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            umma_bf16(d_tmem, umma_desc_sw128(a_base + k * 32), umma_desc_sw128(b_base + k * 32), idesc,
-                      (kb | k) != 0 ? 1u : 0u);
+            if constexpr (CG2)
+              umma_bf16_cg2(d_tmem, umma_desc_sw128(a_base + k * 32), umma_desc_sw128(b_base + k * 32), idesc2,
+                            (kb | k) != 0 ? 1u : 0u);
+            else
+              umma_bf16(d_tmem, umma_desc_sw128(a_base + k * 32), umma_desc_sw128(b_base + k * 32), idesc,
+                        (kb | k) != 0 ? 1u : 0u);
           }
-          if (p.mc) umma_commit_mc(&empty[stage], mc_mask);   // ... in this CTA and in every CTA that also writes it
+          if constexpr (CG2) umma_commit_cg2_mc(&empty[stage], (uint16_t)3);   // both CTAs' producers
+          else if (p.mc) umma_commit_mc(&empty[stage], mc_mask);   // ... in this CTA and in every CTA that also writes it
           else umma_commit(&empty[stage]);  // smem slot reusable once these MMAs retire
-          if (kb == p.total_kb - 1) umma_commit(&tfull[as]);
+          if (kb == p.total_kb - 1) {
+            if constexpr (CG2) umma_commit_cg2_mc(&tfull[as], (uint16_t)3);      // both CTAs' epilogues
+            else umma_commit(&tfull[as]);
+          }
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -815,16 +854,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         else epi_tile<BN, false, false>(p, taddr, stg, lane, cpar, NEW / 4, n_tile, pix_own, stat_slot, &tfull[as], aph);
       }
       tc_fence_before();
-      mbar_arrive(&tempty[as]);
+      if constexpr (CG2) {                      // the even CTA's MMA thread waits for both CTAs' epilogues
+        __syncwarp();
+        if (lane == 0) {
+          if (pair_rank == 0) mbar_arrive(&tempty[as]);
+          else mbar_arrive_remote(&tempty[as], 0);
+        }
+      } else {
+        mbar_arrive(&tempty[as]);
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (p.mc) cluster_sync_all();             // no CTA leaves while its peer may still signal or write into it
+  if (CG2 || p.mc) cluster_sync_all();    // no CTA leaves while its peer may still signal or write into it
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (CG2) tmem_dealloc_cg2(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -912,15 +960,15 @@ void pick_tile(int W, int H, int n, int* tw_, int* th_, int* tn_) {
 
 int num_sms() { return mdx_num_sms(); }
 
-template <int BN, int EPI>
-int launch_tc_epi(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& q, int grid, cudaStream_t st) {
+template <int BN, int EPI, bool CG2>
+int launch_tc_kernel(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& q, int grid, cudaStream_t st) {
   static MdxPerDeviceOnce attr;
   if (attr.need()) {
-    MDX_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MDX_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, CG2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         TcCfg<BN>::SMEM_BYTES));
     attr.mark();
   }
-  if (q.mc) {
+  if (CG2 || q.mc) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(TcCfg<BN>::THREADS);
@@ -928,16 +976,22 @@ int launch_tc_epi(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams
     cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = (unsigned)q.mc; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.x = CG2 ? 2u : (unsigned)q.mc; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    MDX_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, EPI>, maps[0], maps[1], maps[2], mb, q));
+    MDX_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, EPI, CG2>, maps[0], maps[1], maps[2], mb, q));
   } else {
-    gemm_tc_kernel<BN, EPI><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
+    gemm_tc_kernel<BN, EPI, CG2><<<grid, TcCfg<BN>::THREADS, TcCfg<BN>::SMEM_BYTES, st>>>(maps[0], maps[1], maps[2], mb, q);
   }
   g_mdx_launches.fetch_add(1, std::memory_order_relaxed);
   MDX_CHECK_LAUNCH();
   return MDX_OK;
+}
+
+template <int BN, int EPI>
+int launch_tc_epi(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& q, int grid, cudaStream_t st) {
+  if (q.cg2) return launch_tc_kernel<BN, EPI, true>(maps, mb, q, grid, st);
+  return launch_tc_kernel<BN, EPI, false>(maps, mb, q, grid, st);
 }
 
 // How many CTAs of this block shape the device keeps resident when they are launched as clusters of `cs` (a GPC whose
@@ -982,11 +1036,12 @@ int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p,
   int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
   if (p.mc && grid > p.mc_grid_cap) grid = p.mc_grid_cap;
   if (p.mc) grid -= grid % p.mc;            // (num_tiles is a multiple of the cluster size, see mdx_gemm_tc)
+  if (p.cg2) { if (grid > p.mc_grid_cap) grid = p.mc_grid_cap; grid -= grid & 1; }
   TcParams q = p;
   if (const char* dbg = getenv("MDX_GEMM_DEBUG")) q.debug = atoi(dbg);
   const bool no_resident = getenv("MDX_GEMM_NO_RESIDENT") != nullptr;  // A/B switch for tests and profiling
   // weights stay in smem when the whole K fits the B ring and every CTA would otherwise re-fetch them >= 3 times
-  if (!no_resident && p.nseg == 1 && p.seg_taps[0] == 1 && p.total_kb <= TcCfg<BN>::STAGES &&
+  if (!no_resident && !p.cg2 && p.nseg == 1 && p.seg_taps[0] == 1 && p.total_kb <= TcCfg<BN>::STAGES &&
       p.n_tiles_n <= (p.mc ? p.mc_grid_cap : num_sms()) && (long long)p.m_tiles * p.n_tiles_n >= 3ll * num_sms()) {
     q.b_resident = 1;
     const int avail = p.mc && p.mc_grid_cap < num_sms() ? p.mc_grid_cap : num_sms();
@@ -994,6 +1049,10 @@ int launch_tc(const CUtensorMap* maps, const CUtensorMap& mb, const TcParams& p,
     while (p.mc && unit % p.mc) unit += p.n_tiles_n;
     grid = (avail / unit) * unit;
     if (grid == 0) { q.b_resident = 0; grid = p.num_tiles < avail ? p.num_tiles : avail; grid -= p.mc ? grid % p.mc : 0; }
+  }
+  if (q.cg2 && (grid <= 0 || (grid & 1))) {
+    mdx_set_error("mdx_gemm_tc: internal: grid %d does not divide into CTA pairs", grid);
+    return MDX_ERR_INVALID;
   }
   if (q.mc && (grid <= 0 || grid % q.mc)) {
     mdx_set_error("mdx_gemm_tc: internal: grid %d does not divide into clusters of %d", grid, q.mc);
@@ -1170,23 +1229,43 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
     else if (mc_max >= 4 && p.n_tiles_n == 2 && p.num_tiles % 4 == 0) { cs = 4; gn = 2; }
     else if (mc_max >= 2 && p.n_tiles_n % 2 == 0) { cs = 2; gn = 2; }
     int cur = -1;
-    bool ok = cs != 0 && cudaGetDevice(&cur) == cudaSuccess;
+    bool local_ok = cudaGetDevice(&cur) == cudaSuccess;
     auto local = [&](const void* ptr) {
       cudaPointerAttributes pa;
       if (cudaPointerGetAttributes(&pa, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
       return pa.type == cudaMemoryTypeDevice && pa.device == cur;
     };
-    for (int s = 0; ok && s < a->nseg; ++s) ok = local(a->a[s]);
-    if (ok) ok = local(a->b);
-    int cap = 0;
-    for (; ok && cs >= 2; cs >>= 1) {         // a few SMs without partners are a fair price; far fewer is not
+    for (int s = 0; local_ok && s < a->nseg; ++s) local_ok = local(a->a[s]);
+    if (local_ok) local_ok = local(a->b);
+    auto cap_of = [&](int c) {
       switch (bn) {
-        case 64: cap = max_clustered_ctas<64>(cs); break;
-        case 128: cap = max_clustered_ctas<128>(cs); break;
-        case 160: cap = max_clustered_ctas<160>(cs); break;
-        case 192: cap = max_clustered_ctas<192>(cs); break;
-        default: cap = max_clustered_ctas<256>(cs); break;
+        case 64: return max_clustered_ctas<64>(c);
+        case 128: return max_clustered_ctas<128>(c);
+        case 160: return max_clustered_ctas<160>(c);
+        case 192: return max_clustered_ctas<192>(c);
+        default: return max_clustered_ctas<256>(c);
       }
+    };
+    // CTA pairs (tcgen05 cta_group::2) take precedence for convolutions with an even number of m-tiles: two consecutive
+    // m-tiles of one n-tile per cluster, one M = 256 MMA over both SMs, the B block halved between the two CTAs.
+    // Alternating in-process A/B (profiles/r02_gemm_cluster_ab.txt): 3x3 convs -11 .. -17 % against the plain launch
+    // (multicast pairs -2 .. -9 %), 1x1 / dense / GEGLU layers +6 .. +37 % — those never take it.  MDX_GEMM_CG2=0 turns
+    // it off, =1 forces it for every eligible launch; MDX_GEMM_MC=0 turns every cluster form off.
+    const char* cg2_env = getenv("MDX_GEMM_CG2");
+    const bool want_cg2 = cg2_env ? atoi(cg2_env) == 1 : (has_taps && !a->geglu && !(mc_env && atoi(mc_env) == 0));
+    bool ok = local_ok && cs != 0;
+    int cap = 0;
+    if (local_ok && want_cg2 && p.m_tiles % 2 == 0) {
+      const int cap2 = cap_of(2);
+      if (cap2 >= 2 && cap2 * 16 >= num_sms() * 15) {
+        p.cg2 = 1;
+        p.mc_grid_cap = cap2;
+        b_box = bn / 2;
+        ok = false;                           // not both
+      }
+    }
+    for (; ok && cs >= 2; cs >>= 1) {         // a few SMs without partners are a fair price; far fewer is not
+      cap = cap_of(cs);
       if (cap >= cs && cap * 16 >= num_sms() * 15) break;
       gn = 2;                                 // fall back from 4 to pairs along n
     }

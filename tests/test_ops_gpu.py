@@ -115,9 +115,10 @@ def test_gemm_tc_conv3x3_stride2(n, H, W, Cin, Cout):
 @pytest.mark.parametrize("case", ["conv N=320 (2x2 cluster)", "conv N=640 (4x1)", "conv N=960 (pairs)", "1x1 K=320 resident",
                                   "1x1 N=1280 resident 4x1", "stride 2", "geglu", "small image tn=2", "odd m-tiles"])
 def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
-    """The cluster launches (MDX_GEMM_MC: clusters of 4 / 2 / none; every CTA fetches a share of the A — and in 2 x 2
-    clusters of the B — block and multicasts it) change only who loads what: the accumulation order of a tile is the
-    same, so outputs and epilogue statistics must be bit-identical across the three, and right against F.conv2d."""
+    """The cluster launches — multicast clusters (MDX_GEMM_MC: 4 / 2 / none; every CTA fetches a share of the A, and in
+    2 x 2 clusters of the B, block and multicasts it) and CTA pairs (MDX_GEMM_CG2: tcgen05 cta_group::2, one M = 256 MMA
+    over two SMs, B halved between them) — change only who loads and who issues: the accumulation order of an output
+    element is the same, so the results must be bit-identical across the four, and right against F.conv2d."""
     ops = _ops()
     g = torch.Generator().manual_seed(len(case))
     kw = {}
@@ -155,8 +156,13 @@ def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
     if taps == 1:
         xa = xa.view(n * H * W, Cin)
     outs = []
-    for mc in ("4", "2", "0"):
-        monkeypatch.setenv("MDX_GEMM_MC", mc)
+    for mc in ("4", "2", "0", "cg2"):
+        if mc == "cg2":                                   # CTA pairs (tcgen05 cta_group::2), opt-in
+            monkeypatch.setenv("MDX_GEMM_MC", "2")
+            monkeypatch.setenv("MDX_GEMM_CG2", "1")
+        else:
+            monkeypatch.setenv("MDX_GEMM_MC", mc)
+            monkeypatch.setenv("MDX_GEMM_CG2", "0")
         if case == "geglu":
             from minddiffusion_b200.unet import pack_geglu
             wg, bg, gbn = pack_geglu(w.cuda(), torch.zeros(Cout, device="cuda"))
@@ -164,7 +170,7 @@ def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
         else:
             res = torch.randn(ref.numel() // Cout, Cout, generator=g).cuda() if mc == "4" else res
             outs.append(ops.gemm_tc([(xa, taps)], wk.cuda().bfloat16(), out_dtype=torch.float32, residual=res, **kw))
-    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2])
+    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2]) and torch.equal(outs[3], outs[2])
     if case != "geglu":
         assert rel_err(outs[0].cpu().view(ref.shape) - res.cpu().view(ref.shape), ref) < 1e-3
 

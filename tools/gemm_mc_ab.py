@@ -31,7 +31,12 @@ for n, side, K, N, taps, out_t, res_t, geglu, label in SHAPES:
     ms = {v: [] for v in VARIANTS}
     for rnd in range(4):
         for v in VARIANTS:
-            os.environ["MDX_GEMM_MC"] = v
+            if v == "cg2":                      # CTA pairs (tcgen05 cta_group::2)
+                os.environ["MDX_GEMM_MC"] = "2"
+                os.environ["MDX_GEMM_CG2"] = "1"
+            else:
+                os.environ["MDX_GEMM_MC"] = v
+                os.environ["MDX_GEMM_CG2"] = "0"
             run()
             for _ in range(5):
                 flush.zero_()
