@@ -91,11 +91,13 @@ typedef struct mdx_gemm_args {
                   the [n_img, (H-1)/2+1, (W-1)/2+1] output image (size chan_stats with those dimensions).  The taps are
                   strided TMA boxes over the input; no patch matrix is built. */
 } mdx_gemm_args;
-/* Launch form: convolution segments (seg_taps > 1) with an even number of BLOCK_N tiles run as thread-block clusters
-   of two CTAs that fetch each activation block once for both (TMA multicast) — only when every operand is ordinary
-   device memory of the CURRENT device (checked with cudaPointerGetAttributes; anything else, e.g. a mapping of
-   another GPU's memory, takes the plain launch).  Results are bit-identical either way.  MDX_GEMM_MC=0 in the
-   environment disables the cluster form, 2 forces it for every eligible launch. */
+/* Launch form: calls with convolution segments (seg_taps > 1) run as thread-block clusters of two CTAs — as a CTA
+   pair (tcgen05 cta_group::2: two consecutive 128-row tiles, one M = 256 MMA over both SMs, the weight block halved
+   between them) when the number of 128-row tiles is even, else as two CTAs sharing each activation block by TMA
+   multicast — only when every operand is ordinary device memory of the CURRENT device (checked with
+   cudaPointerGetAttributes; anything else, e.g. a mapping of another GPU's memory, takes the plain launch).  Results
+   are bit-identical in all forms.  Environment: MDX_GEMM_CG2=0 disables the CTA-pair form, MDX_GEMM_MC=0 every
+   cluster form. */
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
 /* Statistics slots per image for mdx_gemm_args.chan_stats (0: images too small, use the two-pass GroupNorm). */
 int mdx_gemm_tc_stat_slots(int32_t n_img, int32_t H, int32_t W, int32_t up);
