@@ -171,10 +171,10 @@ class ClockSampler:
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel's largest shape, from the
 # `ncu --set full` capture named in the note (a profiler number, copied here; everything else in the line is live)
-TRAFFIC = {"bytes_per_launch": 633.9e6,
+TRAFFIC = {"bytes_per_launch": 639.2e6,
            "note": "ncu --set full, gemm_tc_kernel conv3x3 C=320 at 64x64, CFG batch 128 (M=524288, N=320, K=2880): "
-                   "337.5 MB read + 296.4 MB written = 633.9 MB DRAM traffic vs 673 MB algorithmic (A once + out once; weights from L2) — no re-reads; "
-                   "profiles/r02_ncu_full_gemm_tc_conv3x3_c320_raw.csv"}
+                   "launched as a CTA pair (gemm_tc_kernel<160, 0, 1>): 337.7 MB read + 301.4 MB written = 639.2 MB DRAM traffic vs 673 MB algorithmic (A once + out once; weights from L2) — no re-reads; "
+                   "profiles/r02_ncu_full_gemm_tc_conv3x3_c320_cg2_raw.csv"}
 
 
 def hbm_probe(torch, ops, dev, B, h, hbm_peak):
