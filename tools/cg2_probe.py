@@ -1,3 +1,6 @@
+"""Smallest check of the three launch forms of mdx_gemm_tc on one 3x3 convolution: plain, multicast pair, CTA pair
+(tcgen05 cta_group::2) — each must run and be bit-identical to the first.  (This is the probe that showed a kernel
+containing cta_group::2 instructions cannot be launched without a cluster: "cluster misconfiguration".)"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
