@@ -96,8 +96,10 @@ typedef struct mdx_gemm_args {
    between them) when the number of 128-row tiles is even, else as two CTAs sharing each activation block by TMA
    multicast — only when every operand is ordinary device memory of the CURRENT device (checked with
    cudaPointerGetAttributes; anything else, e.g. a mapping of another GPU's memory, takes the plain launch).  Results
-   are bit-identical in all forms.  Environment: MDX_GEMM_CG2=0 disables the CTA-pair form, MDX_GEMM_MC=0 every
-   cluster form. */
+   are bit-identical in all forms, except that a CTA-pair launch of ONE plain 3x3 segment (stride 1, tiles inside one
+   image, BLOCK_N 160) loads each input row block once per dx and accumulates the taps dx-outermost: the same sum in
+   another fp32 order (<= 2e-5 relative).  Environment: MDX_GEMM_HALO=0 disables that, MDX_GEMM_CG2=0 the CTA-pair
+   form, MDX_GEMM_MC=0 every cluster form. */
 int mdx_gemm_tc(const mdx_gemm_args* args, void* stream);
 /* Statistics slots per image for mdx_gemm_args.chan_stats (0: images too small, use the two-pass GroupNorm). */
 int mdx_gemm_tc_stat_slots(int32_t n_img, int32_t H, int32_t W, int32_t up);

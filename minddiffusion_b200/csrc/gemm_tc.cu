@@ -68,6 +68,9 @@ struct TcParams {
   int mc_cy, mc_cx;             // the A tile is cut into (tn / mc_sn) x mc_cy x mc_cx sub-boxes of mc_sn x mc_sy x mc_sx
   int mc_sn, mc_sy, mc_sx;      // images x rows x pixels, numbered in row order of the tile
   int mc_grid_cap;  // host only: CTAs the device keeps resident in clusters of this size (the schedule is persistent)
+  int halo;         // CTA-pair form, one 3x3 segment: per (dx, 64-channel block) ONE A box of th + 2 image rows serves the
+  int halo_bytes;   // three dy taps as row-offset views (halo_row_bytes apart) of the same smem — a third to a half of
+  int halo_row_bytes;   // the A traffic; the A ring (3 stages of 32 KiB) and the B ring (6 stages) run on their own barriers
   int cg2;          // 1: clusters of two as a CTA PAIR (tcgen05 cta_group::2): the pair holds two consecutive m-tiles of one
                     // n-tile, the even CTA issues M = 256 MMAs over both SMs, each CTA loads its own A block and half of
                     // the B block (the B map holds BLOCK_N / 2 rows).  Opt-in (MDX_GEMM_CG2=1), excludes mc.
@@ -507,6 +510,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   uint64_t* tempty = tfull + 2;
   uint64_t* bfull = tempty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bfull + 1);
+  // halo mode (CTA-pair instantiations only; their ring leaves room before the epilogue staging): its own rings
+  constexpr int HALO_SA = 3, HALO_SB = 6, HALO_A_STAGE = 32768;
+  uint64_t* ha_full = bfull + 2;           // HALO_SA
+  uint64_t* ha_empty = ha_full + HALO_SA;  // HALO_SA
+  uint64_t* hb_full = ha_empty + HALO_SA;  // HALO_SB
+  uint64_t* hb_empty = hb_full + HALO_SB;  // HALO_SB
+  uint8_t* sBh = smem + HALO_SA * HALO_A_STAGE;
+  static_assert(!CG2 || BN != 160 ||
+                    (HALO_SA * HALO_A_STAGE + HALO_SB * (Cfg::B_STAGE_BYTES / 2) <= Cfg::STAGES_CG2 * (A_STAGE_BYTES + Cfg::B_STAGE_BYTES / 2) &&
+                     Cfg::STAGES_CG2 * (A_STAGE_BYTES + Cfg::B_STAGE_BYTES / 2) + (2 * Cfg::STAGES_CG2 + 7 + 2 * (HALO_SA + HALO_SB)) * 8 <= Cfg::STAGING_OFF),
+                "halo rings");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -528,6 +542,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       mbar_init(&tempty[i], CG2 ? 2 * Cfg::EPI_WARPS : 32 * Cfg::EPI_WARPS);   // pair: one arrival per epilogue warp of both CTAs
     }
     mbar_init(bfull, 1);
+    if constexpr (CG2) {
+      if (p.halo) {
+        for (int i = 0; i < HALO_SA; ++i) { mbar_init(&ha_full[i], 1); mbar_init(&ha_empty[i], 1); }
+        for (int i = 0; i < HALO_SB; ++i) { mbar_init(&hb_full[i], 1); mbar_init(&hb_empty[i], 1); }
+      }
+    }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -602,7 +622,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       // pair: the even CTA's barrier collects both CTAs' bytes (each loads A and half of B)
       const uint32_t stage_tx = CG2 ? 2 * (A_STAGE_BYTES + B_BYTES)
                                       : (p.b_resident ? A_STAGE_BYTES : A_STAGE_BYTES + B_BYTES);
-      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
+      bool halo_done = false;
+      if constexpr (CG2) {
+        if (p.halo) {
+          halo_done = true;
+          int sa = 0, sb = 0;
+          uint32_t pha = 0, phb = 0;
+          const int nkb = p.seg_kb[0];
+          for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
+            const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);
+            const int x0 = (m_tile - m_row * p.tiles_x) * p.tw;
+            const int y0 = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th;
+            const int n0 = (int)fdiv((uint32_t)m_tile, p.fd_tpi);
+            for (int dxi = 0; dxi < 3; ++dxi) {
+              for (int cb = 0; cb < nkb; ++cb) {
+                mbar_wait(&ha_empty[sa], pha ^ 1);
+                if (pair_rank == 0) mbar_arrive_expect_tx(&ha_full[sa], 2u * (uint32_t)p.halo_bytes);
+                tma_load_4d_cg2(smem + sa * HALO_A_STAGE, &tmA0, &ha_full[sa], cb * BK, x0 + dxi - 1, y0 - 1, n0);
+                for (int dyi = 0; dyi < 3; ++dyi) {
+                  mbar_wait(&hb_empty[sb], phb ^ 1);
+                  if (pair_rank == 0) mbar_arrive_expect_tx(&hb_full[sb], 2u * B_BYTES);
+                  tma_load_2d_cg2(sBh + sb * B_BYTES, &tmB, &hb_full[sb], ((dyi * 3 + dxi) * nkb + cb) * BK,
+                                  n_tile * BN + pair_rank * (BN / 2));
+                  if (++sb == HALO_SB) { sb = 0; phb ^= 1; }
+                }
+                if (++sa == HALO_SA) { sa = 0; pha ^= 1; }
+              }
+            }
+          }
+        }
+      }
+      for (int it = 0; !halo_done && tile_at(it, m_tile, n_tile); ++it) {
         const int m_row = (int)fdiv((uint32_t)m_tile, p.fd_tx);
         const int x0 = (m_tile - m_row * p.tiles_x) * p.tw + a_dx;
         const int y0 = (m_row - (int)fdiv((uint32_t)m_row, p.fd_ty) * p.tiles_y) * p.th + a_dy;
@@ -665,7 +715,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         const int rn = rank % gn, rm = rank / gn;
         mc_mask = (uint16_t)((((1u << gn) - 1u) << (rm * gn)) | (((gm == 2 && !p.b_resident) ? (1u | (1u << gn)) : 1u) << rn));
       }
-      for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
+      bool halo_done = false;
+      if constexpr (CG2) {
+        if (p.halo) {
+          halo_done = true;
+          int sa = 0, sb = 0;
+          uint32_t pha = 0, phb = 0;
+          const int nkb = p.seg_kb[0];
+          for (int it = 0; tile_at(it, m_tile, n_tile); ++it, ++iter) {
+            const uint32_t as = iter & 1;
+            const uint32_t aph = (iter >> 1) & 1;
+            mbar_wait(&tempty[as], aph ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + as * BN;
+            uint32_t acc = 0;
+            for (int dxi = 0; dxi < 3; ++dxi) {
+              for (int cb = 0; cb < nkb; ++cb) {
+                mbar_wait(&ha_full[sa], pha);
+                const uint32_t a_base = smem_u32(smem + sa * HALO_A_STAGE);
+                for (int dyi = 0; dyi < 3; ++dyi) {
+                  mbar_wait(&hb_full[sb], phb);
+                  tc_fence_after();
+                  const uint32_t a_view = a_base + (uint32_t)(dyi * p.halo_row_bytes);   // image rows y0 - 1 + dyi ...
+                  const uint32_t b_base = smem_u32(sBh + sb * B_BYTES);
+#pragma unroll
+                  for (int k = 0; k < BK / 16; ++k) {
+                    umma_bf16_cg2(d_tmem, umma_desc_sw128(a_view + k * 32), umma_desc_sw128(b_base + k * 32), idesc2, acc);
+                    acc = 1;
+                  }
+                  umma_commit_cg2_mc(&hb_empty[sb], (uint16_t)3);
+                  if (++sb == HALO_SB) { sb = 0; phb ^= 1; }
+                }
+                umma_commit_cg2_mc(&ha_empty[sa], (uint16_t)3);
+                if (++sa == HALO_SA) { sa = 0; pha ^= 1; }
+              }
+            }
+            umma_commit_cg2_mc(&tfull[as], (uint16_t)3);
+          }
+        }
+      }
+      for (int it = 0; !halo_done && tile_at(it, m_tile, n_tile); ++it, ++iter) {
         const uint32_t as = iter & 1;
         const uint32_t aph = (iter >> 1) & 1;
         if (p.b_resident && it == 0) mbar_wait(bfull, 0);
@@ -1283,6 +1372,19 @@ extern "C" int mdx_gemm_tc(const mdx_gemm_args* a, void* stream) {
       p.mc_sn = btn; p.mc_sy = bth; p.mc_sx = btw;
       p.mc_cy = p.th / bth; p.mc_cx = p.tw / btw;
       if (cs / gn == 2) b_box = bn / 2;       // 2 x 2: the CTAs on the same n-tile fetch half of the B block each
+    }
+  }
+  // Halo boxes (CTA pairs, one plain 3x3 segment, tiles inside one image): the dy taps of a dx share one A box of
+  // th + 2 image rows.  Changes the order in which the taps are accumulated (dx outermost), so results differ from the
+  // other launch forms in the last fp32 bits.  MDX_GEMM_HALO=0 turns it off.
+  if (p.cg2 && a->nseg == 1 && a->seg_taps[0] == 9 && stride == 1 && !a->up_phase && p.tn == 1 && bn == 160 &&
+      p.tw >= 8 && (p.th + 2) * p.tw * 128 <= 32768) {
+    const char* h = getenv("MDX_GEMM_HALO");
+    if (!(h && atoi(h) == 0)) {
+      p.halo = 1;
+      p.halo_row_bytes = p.tw * 128;
+      p.halo_bytes = (p.th + 2) * p.tw * 128;
+      bth = p.th + 2;
     }
   }
   CUtensorMap maps[3];

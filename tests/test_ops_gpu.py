@@ -156,10 +156,11 @@ def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
     if taps == 1:
         xa = xa.view(n * H * W, Cin)
     outs = []
-    for mc in ("4", "2", "0", "cg2"):
-        if mc == "cg2":                                   # CTA pairs (tcgen05 cta_group::2), opt-in
+    for mc in ("4", "2", "0", "cg2", "halo"):
+        if mc in ("cg2", "halo"):                         # CTA pairs (tcgen05 cta_group::2)
             monkeypatch.setenv("MDX_GEMM_MC", "2")
             monkeypatch.setenv("MDX_GEMM_CG2", "1")
+            monkeypatch.setenv("MDX_GEMM_HALO", "1" if mc == "halo" else "0")
         else:
             monkeypatch.setenv("MDX_GEMM_MC", mc)
             monkeypatch.setenv("MDX_GEMM_CG2", "0")
@@ -171,6 +172,8 @@ def test_gemm_tc_cluster_forms_bit_identical(monkeypatch, case):
             res = torch.randn(ref.numel() // Cout, Cout, generator=g).cuda() if mc == "4" else res
             outs.append(ops.gemm_tc([(xa, taps)], wk.cuda().bfloat16(), out_dtype=torch.float32, residual=res, **kw))
     assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2]) and torch.equal(outs[3], outs[2])
+    # halo boxes (plain 3x3 convs in the CTA-pair form) accumulate the taps dx-outermost: same sum, other fp32 order
+    assert rel_err(outs[4], outs[2]) < (1e-2 if case == "geglu" else 2e-5)
     if case != "geglu":
         assert rel_err(outs[0].cpu().view(ref.shape) - res.cpu().view(ref.shape), ref) < 1e-3
 

@@ -31,9 +31,10 @@ for n, side, K, N, taps, out_t, res_t, geglu, label in SHAPES:
     ms = {v: [] for v in VARIANTS}
     for rnd in range(4):
         for v in VARIANTS:
-            if v == "cg2":                      # CTA pairs (tcgen05 cta_group::2)
+            if v in ("cg2", "halo"):            # CTA pairs (tcgen05 cta_group::2), without / with halo boxes
                 os.environ["MDX_GEMM_MC"] = "2"
                 os.environ["MDX_GEMM_CG2"] = "1"
+                os.environ["MDX_GEMM_HALO"] = "1" if v == "halo" else "0"
             else:
                 os.environ["MDX_GEMM_MC"] = v
                 os.environ["MDX_GEMM_CG2"] = "0"
