@@ -173,7 +173,7 @@ class ClockSampler:
 # `ncu --set full` capture named in the note (a profiler number, copied here; everything else in the line is live)
 TRAFFIC = {"bytes_per_launch": 639.2e6,
            "note": "ncu --set full, gemm_tc_kernel conv3x3 C=320 at 64x64, CFG batch 128 (M=524288, N=320, K=2880): "
-                   "launched as a CTA pair (gemm_tc_kernel<160, 0, 1>): 337.7 MB read + 301.4 MB written = 639.2 MB DRAM traffic vs 673 MB algorithmic (A once + out once; weights from L2) — no re-reads; "
+                   "launched as a CTA pair (gemm_tc_kernel<160, 0, 1>, captured before the halo boxes, which change L2 -> SM traffic, not DRAM traffic): 337.7 MB read + 301.4 MB written = 639.2 MB DRAM traffic vs 673 MB algorithmic (A once + out once; weights from L2) — no re-reads; "
                    "profiles/r02_ncu_full_gemm_tc_conv3x3_c320_cg2_raw.csv"}
 
 
